@@ -1,0 +1,164 @@
+/* b200xf — C ABI of the B200-native data-parallel Transformer train step.
+ *
+ * The reference (ddrakard/tensorflow-distributed-on-gke) has no FFI: its boundary for this path is the
+ * Python call surface that distributed_training_transformer/__main__.py uses.  Each entry point below
+ * names the reference code it stands in for (paths relative to
+ * /root/reference/distributed_training_transformer/).  A Python façade with the reference's own names
+ * sits on top of this ABI; a TF custom-op wrapper would bind the same symbols.
+ *
+ * Conventions: every function returns 0 on success and non-zero on failure, after which
+ * b200xf_last_error() (thread-local) describes the problem.  Tokens are int64, row-major [batch, seq],
+ * PAD = 0 (transformer_model.py:12,22,60).  Dense kernels are [in, out] (y = xW + b).  All device work is
+ * enqueued on the context's stream and is asynchronous unless stated.  A context is not thread-safe;
+ * distinct contexts are independent (one per GPU / process, as one TF worker per pod in the reference).
+ */
+#ifndef B200XF_H_
+#define B200XF_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200xf_ctx b200xf_ctx;
+
+/* Constructor arguments of transformer_model.py:319-323 `Transformer(...)` plus the optimizer/schedule
+ * constants of __main__.py:58,72-73. */
+typedef struct b200xf_hparams {
+  int32_t layers_count;
+  int32_t embedding_size;
+  int32_t heads_count;
+  int32_t feed_forward_hidden_size;
+  int32_t input_vocabulary_size;
+  int32_t target_vocabulary_size;
+  int32_t maximum_input_length;
+  int32_t maximum_target_length;
+  float droput_rate;      /* sic — the reference's keyword (transformer_model.py:323) */
+  float adam_beta_1;      /* __main__.py:73 (0.9)  */
+  float adam_beta_2;      /* __main__.py:73 (0.98) */
+  float adam_epsilon;     /* __main__.py:73 (1e-9) */
+  int32_t warmup_steps;   /* __main__.py:58 (4000) */
+  int32_t max_tokens;     /* capacity: max(batch*seq) of any call, source or target side */
+} b200xf_hparams;
+
+const char* b200xf_last_error(void);
+int b200xf_version(void);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+long long b200xf_launch_count(void);
+
+/* ---- model state: Transformer.__init__ + build_model (transformer_model.py:318-333,366-371) ---------- */
+int b200xf_ctx_create(const b200xf_hparams* hp, int device, void* cuda_stream, b200xf_ctx** out);
+int b200xf_ctx_destroy(b200xf_ctx* ctx);
+
+/* model.trainable_variables / load_weights / save_weights (__main__.py:87,112-114; checkpoint.py:86):
+ * the variables live in one flat fp32 device buffer; entry i is a [rows, cols] view (cols == 1-D length
+ * for vectors, rows == 1) at element `offset` with row pitch `ld`.  Names are the Keras object-graph keys
+ * of saved_weights/<n>/model_weights.index.  grad / adam_m / adam_v buffers share the same layout. */
+int b200xf_param_count(b200xf_ctx* ctx);
+int b200xf_param_info(b200xf_ctx* ctx, int index, char* name_buf, size_t name_buf_len, int64_t* rows, int64_t* cols,
+                      int64_t* ld, int64_t* offset, int32_t* ndim);
+int64_t b200xf_param_total(b200xf_ctx* ctx);
+float* b200xf_param_ptr(b200xf_ctx* ctx);
+float* b200xf_grad_ptr(b200xf_ctx* ctx);
+float* b200xf_adam_m_ptr(b200xf_ctx* ctx);
+float* b200xf_adam_v_ptr(b200xf_ctx* ctx);
+/* Must be called after the host writes into param_ptr (refreshes the bf16 operand copy the GEMMs read). */
+int b200xf_params_changed(b200xf_ctx* ctx);
+/* optimizer.iterations (__main__.py:72-73,113-114) */
+int b200xf_set_iterations(b200xf_ctx* ctx, int64_t iterations);
+int b200xf_get_iterations(b200xf_ctx* ctx, int64_t* iterations);
+
+/* ---- Transformer.call (transformer_model.py:335-348), training=False/True with dropout 0 ------------
+ * inp [B,S], tgt_in [B,T] int64 DEVICE pointers; logits_out fp32 [B,T,V] DEVICE pointer or NULL. */
+int b200xf_forward(b200xf_ctx* ctx, const int64_t* inp, const int64_t* tgt_in, int B, int S, int T, int training,
+                   float* logits_out);
+
+/* ---- train_step (__main__.py:105-117): shift, forward, local_loss_function(.., workers_count), backward,
+ * gradient all-reduce when a communicator is attached (cluster/cluster.py:66), Adam + schedule in place,
+ * accuracy counts.  inp [B,S], target [B,T+1] int64.  out3 = {loss (already / workers_count),
+ * accuracy numerator, accuracy denominator} fp32.
+ *   _device : DEVICE token pointers, DEVICE out3, fully asynchronous.
+ *   _host   : HOST token pointers (pinned for async copies), HOST out3; copies in, runs, copies the three
+ *             scalars back and synchronises the stream — the reference-facing call. */
+int b200xf_train_step_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T_plus_1,
+                             int workers_count, float* out3);
+int b200xf_train_step_host(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T_plus_1,
+                           int workers_count, float* out3);
+/* test_step (__main__.py:119-125): forward + loss(workers_count=1) + accuracy, no update.  DEVICE pointers. */
+int b200xf_eval_step_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T_plus_1,
+                            float* out3);
+/* Run only forward+loss+backward (no all-reduce, no Adam): gradients are left in grad_ptr. */
+int b200xf_forward_backward_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T_plus_1,
+                                   int workers_count, float* out3);
+int b200xf_synchronize(b200xf_ctx* ctx);
+
+/* ---- MultiWorkerMirroredStrategy's implicit SUM all-reduce (cluster/cluster.py:66; __main__.py:113-114,
+ * 131-132): NCCL over NVLink, one rank per process/GPU.  unique_id is the 128-byte ncclUniqueId obtained
+ * from b200xf_comm_unique_id on rank 0 and broadcast by the caller. */
+int b200xf_comm_unique_id(void* unique_id_128_bytes);
+int b200xf_comm_init(b200xf_ctx* ctx, const void* unique_id_128_bytes, int rank, int world);
+int b200xf_comm_destroy(b200xf_ctx* ctx);
+/* All-reduce (SUM, fp32, in place) of `count` floats at DEVICE pointer on the context's comm stream. */
+int b200xf_allreduce_bucket(b200xf_ctx* ctx, float* device_ptr, int64_t count);
+
+/* ---- per-kernel entry points (unit tests, ncu).  All pointers are DEVICE pointers, `stream` a cudaStream_t. */
+
+/* tf.keras.layers.Dense matmul and its gradients (transformer_model.py:119-122,169-175,333):
+ * D[M,N] = alpha * A . B^T-like product, bf16 inputs, fp32 accumulate on tcgen05 tensor cores.
+ *   a_mn=0: A stored [M][K] (ld=lda); a_mn=1: stored [K][M].   b_mn=0: B stored [N][K]; b_mn=1: stored [K][N].
+ *   bias fp32 [N] or NULL; relu!=0 applies max(0,.); resid bf16 [M][ldr] with resid_op 1 (add) or 2 (zero
+ *   where resid<=0); d_fp32!=0 writes fp32; accumulate!=0 atomically adds into fp32 D (split-K allowed). */
+int b200xf_gemm_bf16(const void* a, int lda, int a_mn, const void* b, int ldb, int b_mn, void* d, int ldd, int d_fp32,
+                     int accumulate, int M, int N, int K, const float* bias, int relu, const void* resid, int ldr,
+                     int resid_op, float alpha, int force_bn, int split_k, void* stream);
+
+/* scaled_dot_product_attention + masks + split/merge heads (transformer_model.py:56-70,73-109,124-131,160-163).
+ * q [B*Sq, ldq], k/v [B*Sk, ld*], o [B*Sq, ldo] bf16, head h in columns [h*dk,(h+1)*dk); key_tokens [B,Sk] int64;
+ * lse fp32 [B,H,Sq] (log2 domain). */
+int b200xf_attention_fwd(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, void* o, int ldo,
+                         float* lse, const int64_t* key_tokens, int causal, int B, int H, int Sq, int Sk, int dk,
+                         void* stream);
+int b200xf_attention_bwd(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, const void* o, int ldo,
+                         const float* lse, const int64_t* key_tokens, int causal, int B, int H, int Sq, int Sk, int dk,
+                         const void* d_o, int lddo, void* dq, int lddq, void* dk_out, int lddk, void* dv_out, int lddv,
+                         float* delta_scratch, void* stream);
+
+/* LayerNormalization(epsilon) of (x + resid) (transformer_model.py:187-188,198,204).  bf16 rows of length d.
+ * z_out (optional) receives x+resid; mean/rstd fp32 [rows]. */
+int b200xf_layernorm_residual_fwd(const void* x, const void* resid, const float* gamma, const float* beta, void* y,
+                                  void* z_out, float* mean, float* rstd, int rows, int d, float eps, void* stream);
+/* Backward.  dcol (optional) = column sums of dz.  scratch: b200xf_layernorm_bwd_scratch_bytes(rows, d) bytes of
+ * device memory whose last 4 bytes (a counter) must be zero on entry; they are zero again on return. */
+size_t b200xf_layernorm_bwd_scratch_bytes(int rows, int d);
+int b200xf_layernorm_residual_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const float* gamma,
+                                  void* dz, float* dgamma, float* dbeta, float* dcol, int rows, int d, void* scratch,
+                                  void* stream);
+
+/* Embedding lookup * sqrt(d) + positional encoding (transformer_model.py:273-275,305-307) and its gradient. */
+int b200xf_embed_pe_fwd(const int64_t* tokens, const float* table, int vocab, const float* pe, void* out, int B, int S,
+                        int d, void* stream);
+size_t b200xf_embed_bwd_scratch_bytes(int n_tokens);
+int b200xf_embed_pe_bwd(const int64_t* tokens, const void* dx, float* dtable, int vocab, int n_tokens, int d,
+                        void* scratch, size_t scratch_bytes, void* stream);
+
+/* loss_object + local_loss_function + accuracy_function (transformer_model.py:7-26) over bf16 logits
+ * [rows, ldl]; overwrites logits with d(loss)/d(logits) when write_grad != 0.  out3 = {loss, acc_num, acc_den}.
+ * scratch: rows * 8 + 16 bytes. */
+int b200xf_vocab_ce_fwd_bwd(void* logits, int ldl, const int64_t* labels, int rows, int V, int workers_count,
+                            int write_grad, float* out3, void* scratch, void* stream);
+
+/* tf.keras.optimizers.Adam(TransformerLearningRateSchedule(d), beta_1, beta_2, epsilon) applied to a flat range
+ * (__main__.py:56-73,113-114).  iterations_dev: DEVICE int64 holding optimizer.iterations before the step. */
+int b200xf_adam_step(float* w, float* g, float* m, float* v, void* w_bf16_or_null, int64_t n,
+                     const int64_t* iterations_dev, int embedding_size, int warmup_steps, float beta_1, float beta_2,
+                     float epsilon, int zero_grad, void* stream);
+
+/* positional_encoding (transformer_model.py:29-53) computed on the host in fp32: out [positions, d]. */
+int b200xf_positional_encoding_host(float* out, int positions, int d);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200XF_H_ */

@@ -1,0 +1,39 @@
+// Error reporting and small process-wide bookkeeping shared by all translation units.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+
+#include "internal.h"
+
+namespace b200xf {
+
+namespace {
+thread_local char g_error[1024] = "";
+std::atomic<long long> g_launches{0};
+}  // namespace
+
+int set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+  return 1;
+}
+const char* last_error_string() { return g_error; }
+
+int num_sms() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+long long launches_total() { return g_launches.load(std::memory_order_relaxed); }
+
+}  // namespace b200xf

@@ -1,0 +1,673 @@
+// Model state + one-step orchestration: the C++ counterpart of Transformer.__init__/call
+// (transformer_model.py:318-348) and train_step (__main__.py:105-117) over the CUDA kernels.
+//
+// HBM layout.  All trainable variables live in ONE flat fp32 buffer (with identically laid out grad /
+// Adam-m / Adam-v buffers and a bf16 operand copy), ordered in reverse forward order so that backward
+// completes contiguous ranges from the front: final_layer, decoder layers L-1..0, decoder embedding,
+// the cross-attention K|V projections of ALL decoder layers fused into one [d, L*2d] matrix, encoder
+// layers L-1..0, encoder embedding.  Q|K|V of each self-attention is one fused [d, 3d] matrix.  The
+// reference's 172 logical variables (saved_weights/*/model_weights.index) are exposed as strided views.
+#include "context.h"
+
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <cmath>
+#include <cstring>
+
+namespace b200xf {
+
+namespace {
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+constexpr size_t kAlignElems = 64;  // every tensor starts on a 256-byte boundary (fp32)
+}  // namespace
+
+// ------------------------------------------------------------------------------------ NCCL (dlopen)
+struct NcclApi {
+  void* handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+
+static NcclApi* nccl_api() {
+  static NcclApi api;
+  static bool tried = false;
+  if (tried) return api.handle ? &api : nullptr;
+  tried = true;
+  const char* env = getenv("B200XF_NCCL_LIB");
+  const char* names[] = {env, "libnccl.so.2", "libnccl.so"};
+  for (const char* n : names) {
+    if (!n) continue;
+    api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (api.handle) break;
+  }
+  if (!api.handle) return nullptr;
+#define LOAD(field, sym) api.field = reinterpret_cast<decltype(api.field)>(dlsym(api.handle, sym))
+  LOAD(GetUniqueId, "ncclGetUniqueId"); LOAD(CommInitRank, "ncclCommInitRank"); LOAD(CommDestroy, "ncclCommDestroy");
+  LOAD(AllReduce, "ncclAllReduce"); LOAD(GroupStart, "ncclGroupStart"); LOAD(GroupEnd, "ncclGroupEnd");
+  LOAD(GetErrorString, "ncclGetErrorString");
+#undef LOAD
+  if (!api.GetUniqueId || !api.CommInitRank || !api.AllReduce || !api.CommDestroy) { api.handle = nullptr; return nullptr; }
+  return &api;
+}
+
+#define B200XF_NCCL(expr)                                                                               \
+  do {                                                                                                  \
+    ncclResult_t _r = (expr);                                                                           \
+    if (_r != ncclSuccess) return set_error("%s: %s", #expr, nccl_api()->GetErrorString ? nccl_api()->GetErrorString(_r) : "nccl error"); \
+  } while (0)
+
+int comm_unique_id(void* out128) {
+  NcclApi* api = nccl_api();
+  if (!api) return set_error("NCCL library not found (set B200XF_NCCL_LIB)");
+  ncclUniqueId id;
+  B200XF_NCCL(api->GetUniqueId(&id));
+  memcpy(out128, &id, sizeof(id));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------ layout
+size_t Context::add_tensor(size_t& cursor, size_t elems) {
+  const size_t off = cursor;
+  cursor = align_up(cursor + elems, kAlignElems);
+  return off;
+}
+
+Dense Context::add_dense(size_t& cursor, int K, int N, int ld) {
+  Dense p; p.K = K; p.N = N; p.ld = ld;
+  p.w = add_tensor(cursor, size_t(K) * ld);
+  p.b = add_tensor(cursor, size_t(ld));
+  return p;
+}
+
+void Context::add_view(const std::string& name, size_t offset, int64_t rows, int64_t cols, int64_t ld, int ndim) {
+  views[name] = ParamView{name, rows, cols, ld, int64_t(offset), ndim};
+}
+
+void Context::build_layout() {
+  const int L = hp.layers_count, d = hp.embedding_size, dff = hp.feed_forward_hidden_size;
+  const int Vin = hp.input_vocabulary_size, Vt = hp.target_vocabulary_size;
+  vt_ld = int(align_up(size_t(Vt), 8));
+  size_t cur = 0;
+  sections.clear();
+  auto close_section = [&](size_t begin) { sections.push_back({begin, cur}); };
+
+  size_t begin = cur;
+  final_layer = add_dense(cur, d, Vt, vt_ld);
+  add_view("final_layer/kernel", final_layer.w, d, Vt, vt_ld, 2);
+  add_view("final_layer/bias", final_layer.b, 1, Vt, vt_ld, 1);
+  close_section(begin);
+
+  dec.resize(L); enc.resize(L);
+  auto ln = [&](LnP& p, const std::string& prefix) {
+    p.g = add_tensor(cur, d); p.b = add_tensor(cur, d);
+    add_view(prefix + "/gamma", p.g, 1, d, d, 1); add_view(prefix + "/beta", p.b, 1, d, d, 1);
+  };
+  auto dense_views = [&](const Dense& p, const std::string& prefix) {
+    add_view(prefix + "/kernel", p.w, p.K, p.N, p.ld, 2); add_view(prefix + "/bias", p.b, 1, p.N, p.ld, 1);
+  };
+  auto qkv_views = [&](const Dense& p, const std::string& prefix) {
+    const char* names[3] = {"query_generator_weights", "key_generator_weights", "value_generator_weights"};
+    for (int i = 0; i < 3; ++i) {
+      add_view(prefix + "/" + names[i] + "/kernel", p.w + size_t(i) * d, d, d, p.ld, 2);
+      add_view(prefix + "/" + names[i] + "/bias", p.b + size_t(i) * d, 1, d, d, 1);
+    }
+  };
+  for (int l = L - 1; l >= 0; --l) {
+    begin = cur;
+    DecLayer& y = dec[l];
+    const std::string p = "decoder/decoder_layers/" + std::to_string(l);
+    y.f2 = add_dense(cur, dff, d, d); dense_views(y.f2, p + "/ffn/layer_with_weights-1");
+    y.f1 = add_dense(cur, d, dff, dff); dense_views(y.f1, p + "/ffn/layer_with_weights-0");
+    ln(y.ln3, p + "/layernorm3");
+    y.o2 = add_dense(cur, d, d, d); dense_views(y.o2, p + "/mha2/dense");
+    y.q2 = add_dense(cur, d, d, d); dense_views(y.q2, p + "/mha2/query_generator_weights");
+    ln(y.ln2, p + "/layernorm2");
+    y.o1 = add_dense(cur, d, d, d); dense_views(y.o1, p + "/mha1/dense");
+    y.qkv1 = add_dense(cur, d, 3 * d, 3 * d); qkv_views(y.qkv1, p + "/mha1");
+    ln(y.ln1, p + "/layernorm1");
+    close_section(begin);
+  }
+  begin = cur;
+  dec_emb = add_tensor(cur, size_t(Vt) * d);
+  add_view("decoder/embedding/embeddings", dec_emb, Vt, d, d, 2);
+  kv_all = add_dense(cur, d, L * 2 * d, L * 2 * d);
+  for (int l = 0; l < L; ++l) {
+    const std::string p = "decoder/decoder_layers/" + std::to_string(l) + "/mha2";
+    add_view(p + "/key_generator_weights/kernel", kv_all.w + size_t(l) * 2 * d, d, d, kv_all.ld, 2);
+    add_view(p + "/key_generator_weights/bias", kv_all.b + size_t(l) * 2 * d, 1, d, d, 1);
+    add_view(p + "/value_generator_weights/kernel", kv_all.w + size_t(l) * 2 * d + d, d, d, kv_all.ld, 2);
+    add_view(p + "/value_generator_weights/bias", kv_all.b + size_t(l) * 2 * d + d, 1, d, d, 1);
+  }
+  close_section(begin);
+  for (int l = L - 1; l >= 0; --l) {
+    begin = cur;
+    EncLayer& y = enc[l];
+    const std::string p = "encoder/encoder_layers/" + std::to_string(l);
+    y.f2 = add_dense(cur, dff, d, d); dense_views(y.f2, p + "/ffn/layer_with_weights-1");
+    y.f1 = add_dense(cur, d, dff, dff); dense_views(y.f1, p + "/ffn/layer_with_weights-0");
+    ln(y.ln2, p + "/layernorm2");
+    y.o = add_dense(cur, d, d, d); dense_views(y.o, p + "/mha/dense");
+    y.qkv = add_dense(cur, d, 3 * d, 3 * d); qkv_views(y.qkv, p + "/mha");
+    ln(y.ln1, p + "/layernorm1");
+    close_section(begin);
+  }
+  begin = cur;
+  enc_emb = add_tensor(cur, size_t(Vin) * d);
+  add_view("encoder/embedding/embeddings", enc_emb, Vin, d, d, 2);
+  close_section(begin);
+  total_params = cur;
+
+  // logical table in the physical order of the reference's data shard
+  table.clear();
+  auto push = [&](const std::string& n) { table.push_back(views.at(n)); };
+  push("final_layer/kernel"); push("final_layer/bias");
+  push("encoder/embedding/embeddings"); push("decoder/embedding/embeddings");
+  for (int l = 0; l < L; ++l)
+    for (const char* s : {"layernorm1", "layernorm2"}) {
+      push("encoder/encoder_layers/" + std::to_string(l) + "/" + s + "/gamma");
+      push("encoder/encoder_layers/" + std::to_string(l) + "/" + s + "/beta");
+    }
+  for (int l = 0; l < L; ++l)
+    for (const char* s : {"layernorm1", "layernorm2", "layernorm3"}) {
+      push("decoder/decoder_layers/" + std::to_string(l) + "/" + s + "/gamma");
+      push("decoder/decoder_layers/" + std::to_string(l) + "/" + s + "/beta");
+    }
+  auto mha = [&](const std::string& p) {
+    for (const char* s : {"query_generator_weights", "key_generator_weights", "value_generator_weights", "dense"}) {
+      push(p + "/" + s + "/kernel"); push(p + "/" + s + "/bias");
+    }
+  };
+  auto ffn = [&](const std::string& p) {
+    for (const char* s : {"layer_with_weights-0", "layer_with_weights-1"}) { push(p + "/ffn/" + s + "/kernel"); push(p + "/ffn/" + s + "/bias"); }
+  };
+  for (int l = 0; l < L; ++l) { const std::string p = "encoder/encoder_layers/" + std::to_string(l); mha(p + "/mha"); ffn(p); }
+  for (int l = 0; l < L; ++l) { const std::string p = "decoder/decoder_layers/" + std::to_string(l); mha(p + "/mha1"); mha(p + "/mha2"); ffn(p); }
+}
+
+// ------------------------------------------------------------------------------------ create / destroy
+void positional_encoding_host(float* out, int positions, int d) {
+  // transformer_model.py:29-53, evaluated in fp32 like the TF ops it restates.
+  for (int p = 0; p < positions; ++p)
+    for (int i = 0; i < d; ++i) {
+      const float expo = float(2 * (i / 2)) / float(d);
+      const float rate = 1.0f / powf(10000.0f, expo);
+      const float ang = float(p) * rate;
+      out[size_t(p) * d + i] = (i & 1) ? cosf(ang) : sinf(ang);
+    }
+}
+
+template <typename T>
+int Context::arena_alloc(T** out, size_t count) {
+  const size_t bytes = align_up(count * sizeof(T), 256);
+  if (arena_used + bytes > arena_size) return set_error("workspace arena exhausted (%zu + %zu > %zu)", arena_used, bytes, arena_size);
+  *out = reinterpret_cast<T*>(arena + arena_used);
+  arena_used += bytes;
+  return 0;
+}
+
+int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
+  hp = h; device = dev; stream = s;
+  const int L = hp.layers_count, d = hp.embedding_size, H = hp.heads_count, dff = hp.feed_forward_hidden_size;
+  if (L <= 0 || d <= 0 || H <= 0 || dff <= 0) return set_error("invalid hyper-parameters");
+  if (d % H) return set_error("embedding_size %% heads_count != 0 (transformer_model.py:117)");
+  const int dk = d / H;
+  if (dk != 16 && dk != 32 && dk != 64) return set_error("head size %d unsupported (16, 32 or 64)", dk);
+  if (d % 8 || dff % 8 || d > 2048) return set_error("embedding_size and feed_forward_hidden_size must be multiples of 8 (d <= 2048)");
+  if (hp.droput_rate != 0.f) return set_error("dropout rate %g: only rate 0 is implemented in this build", hp.droput_rate);
+  if (hp.max_tokens <= 0) return set_error("max_tokens must be positive");
+  B200XF_CUDA(cudaSetDevice(device));
+  build_layout();
+  const size_t P = total_params;
+  B200XF_CUDA(cudaMalloc(&params, P * sizeof(float)));
+  B200XF_CUDA(cudaMalloc(&grads, P * sizeof(float)));
+  B200XF_CUDA(cudaMalloc(&adam_m, P * sizeof(float)));
+  B200XF_CUDA(cudaMalloc(&adam_v, P * sizeof(float)));
+  B200XF_CUDA(cudaMalloc(&shadow, P * sizeof(bf16)));
+  B200XF_CUDA(cudaMemsetAsync(params, 0, P * sizeof(float), stream));
+  B200XF_CUDA(cudaMemsetAsync(grads, 0, P * sizeof(float), stream));
+  B200XF_CUDA(cudaMemsetAsync(adam_m, 0, P * sizeof(float), stream));
+  B200XF_CUDA(cudaMemsetAsync(adam_v, 0, P * sizeof(float), stream));
+  B200XF_CUDA(cudaMemsetAsync(shadow, 0, P * sizeof(bf16), stream));
+  grads_clean = true;
+
+  // ---- workspace arena
+  const size_t N = size_t(hp.max_tokens);
+  const size_t nd = N * d, nff = N * dff;
+  const size_t ln_scr = ln_bwd_scratch_floats(int(N), d);
+  emb_scratch_bytes = embed_bwd_scratch_bytes(int(N));
+  size_t bytes = 0;
+  auto need = [&](size_t count, size_t elt) { bytes += align_up(count * elt, 256); };
+  // encoder: x (L+1), qkv, ctx, z1, o1, h, z2, lse, 4 stats
+  need(nd * (L + 1), 2);
+  for (int l = 0; l < L; ++l) { need(3 * nd, 2); need(nd, 2); need(nd, 2); need(nd, 2); need(nff, 2); need(nd, 2); need(N * H, 4); need(4 * N, 4); }
+  // decoder: x (L+1), qkv, ctx1, z1, o1, q2, ctx2, z2, o2, h, z3, lse1, lse2, 6 stats
+  need(nd * (L + 1), 2);
+  for (int l = 0; l < L; ++l) { need(3 * nd, 2); for (int i = 0; i < 8; ++i) need(nd, 2); need(nff, 2); need(2 * N * H, 4); need(6 * N, 4); }
+  need(N * size_t(L) * 2 * d, 2); need(N * size_t(L) * 2 * d, 2);   // kv_all, dkv_all
+  need(N * size_t(vt_ld), 2);                                       // logits / dlogits
+  for (int i = 0; i < 5; ++i) need(nd, 2);                          // dA dB dz dctx dq2
+  need(nff, 2); need(3 * nd, 2);                                    // dh dqkv
+  need(N * H, 4);                                                   // delta
+  for (int i = 0; i < 4; ++i) need(N + 64, 8);                      // inp, target, tgt_in, labels
+  need(N, 4); need(N, 4);                                           // row_loss, row_correct
+  need(ln_scr + 64, 4); need(emb_scratch_bytes, 1);
+  need(size_t(hp.maximum_input_length) * d, 4); need(size_t(hp.maximum_target_length) * d, 4);
+  need(1024, 1);
+  arena_size = bytes + (1 << 20);
+  B200XF_CUDA(cudaMalloc(&arena, arena_size));
+  B200XF_CUDA(cudaMemsetAsync(arena, 0, arena_size, stream));
+  arena_used = 0;
+
+  B200XF_TRY(arena_alloc(&enc_x, nd * (L + 1)));
+  ea.resize(L);
+  for (int l = 0; l < L; ++l) {
+    EncAct& a = ea[l];
+    B200XF_TRY(arena_alloc(&a.qkv, 3 * nd)); B200XF_TRY(arena_alloc(&a.ctx, nd)); B200XF_TRY(arena_alloc(&a.z1, nd));
+    B200XF_TRY(arena_alloc(&a.o1, nd)); B200XF_TRY(arena_alloc(&a.h, nff)); B200XF_TRY(arena_alloc(&a.z2, nd));
+    B200XF_TRY(arena_alloc(&a.lse, N * H)); B200XF_TRY(arena_alloc(&a.stats, 4 * N));
+  }
+  B200XF_TRY(arena_alloc(&dec_x, nd * (L + 1)));
+  da.resize(L);
+  for (int l = 0; l < L; ++l) {
+    DecAct& a = da[l];
+    B200XF_TRY(arena_alloc(&a.qkv, 3 * nd)); B200XF_TRY(arena_alloc(&a.ctx1, nd)); B200XF_TRY(arena_alloc(&a.z1, nd));
+    B200XF_TRY(arena_alloc(&a.o1, nd)); B200XF_TRY(arena_alloc(&a.q2, nd)); B200XF_TRY(arena_alloc(&a.ctx2, nd));
+    B200XF_TRY(arena_alloc(&a.z2, nd)); B200XF_TRY(arena_alloc(&a.o2, nd)); B200XF_TRY(arena_alloc(&a.z3, nd));
+    B200XF_TRY(arena_alloc(&a.h, nff)); B200XF_TRY(arena_alloc(&a.lse1, N * H)); B200XF_TRY(arena_alloc(&a.lse2, N * H));
+    B200XF_TRY(arena_alloc(&a.stats, 6 * N));
+  }
+  B200XF_TRY(arena_alloc(&kv, N * size_t(L) * 2 * d)); B200XF_TRY(arena_alloc(&dkv, N * size_t(L) * 2 * d));
+  B200XF_TRY(arena_alloc(&logits, N * size_t(vt_ld)));
+  B200XF_TRY(arena_alloc(&dA, nd)); B200XF_TRY(arena_alloc(&dB, nd)); B200XF_TRY(arena_alloc(&dz, nd));
+  B200XF_TRY(arena_alloc(&dctx, nd)); B200XF_TRY(arena_alloc(&dq2, nd));
+  B200XF_TRY(arena_alloc(&dh, nff)); B200XF_TRY(arena_alloc(&dqkv, 3 * nd));
+  B200XF_TRY(arena_alloc(&delta, N * H));
+  B200XF_TRY(arena_alloc(&tok_inp, N + 64)); B200XF_TRY(arena_alloc(&tok_target, N + 64));
+  B200XF_TRY(arena_alloc(&tok_tgt_in, N + 64)); B200XF_TRY(arena_alloc(&tok_labels, N + 64));
+  B200XF_TRY(arena_alloc(&row_loss, N)); B200XF_TRY(arena_alloc(&row_correct, N));
+  B200XF_TRY(arena_alloc(&ln_scratch, ln_scr + 64));
+  B200XF_TRY(arena_alloc(&emb_scratch, emb_scratch_bytes));
+  B200XF_TRY(arena_alloc(&pe_in, size_t(hp.maximum_input_length) * d));
+  B200XF_TRY(arena_alloc(&pe_tgt, size_t(hp.maximum_target_length) * d));
+  char* small = nullptr;
+  B200XF_TRY(arena_alloc(&small, 1024));
+  iterations_dev = reinterpret_cast<long long*>(small);
+  nonpad_count = reinterpret_cast<int*>(small + 64);
+  ln_counter = reinterpret_cast<unsigned*>(small + 128);
+  metrics = reinterpret_cast<float*>(small + 256);      // 3 local + 3 reduced
+
+  {
+    std::vector<float> pe(size_t(std::max(hp.maximum_input_length, hp.maximum_target_length)) * d);
+    positional_encoding_host(pe.data(), hp.maximum_input_length, d);
+    B200XF_CUDA(cudaMemcpyAsync(pe_in, pe.data(), size_t(hp.maximum_input_length) * d * 4, cudaMemcpyHostToDevice, stream));
+    B200XF_CUDA(cudaStreamSynchronize(stream));
+    positional_encoding_host(pe.data(), hp.maximum_target_length, d);
+    B200XF_CUDA(cudaMemcpyAsync(pe_tgt, pe.data(), size_t(hp.maximum_target_length) * d * 4, cudaMemcpyHostToDevice, stream));
+    B200XF_CUDA(cudaStreamSynchronize(stream));
+  }
+  adam.beta1 = hp.adam_beta_1; adam.beta2 = hp.adam_beta_2; adam.eps = hp.adam_epsilon;
+  adam.rsqrt_d_model = 1.0f / sqrtf(float(d));
+  adam.warmup_pow_m15 = float(pow(double(hp.warmup_steps), -1.5));
+  B200XF_CUDA(cudaMallocHost(&host_out, 64));
+  B200XF_CUDA(cudaStreamCreateWithFlags(&comm_stream, cudaStreamNonBlocking));
+  B200XF_CUDA(cudaEventCreateWithFlags(&ev_ready, cudaEventDisableTiming));
+  B200XF_CUDA(cudaEventCreateWithFlags(&ev_done, cudaEventDisableTiming));
+  return 0;
+}
+
+Context::~Context() {
+  if (comm) comm_destroy();
+  cudaSetDevice(device);
+  if (stream) cudaStreamSynchronize(stream);
+  cudaFree(params); cudaFree(grads); cudaFree(adam_m); cudaFree(adam_v); cudaFree(shadow); cudaFree(arena);
+  if (host_out) cudaFreeHost(host_out);
+  if (comm_stream) cudaStreamDestroy(comm_stream);
+  if (ev_ready) cudaEventDestroy(ev_ready);
+  if (ev_done) cudaEventDestroy(ev_done);
+  gemm_clear_tensor_map_cache();
+}
+
+int Context::params_changed() { return cast_f32_to_bf16(params, shadow, total_params, stream); }
+
+int Context::set_iterations(long long it) {
+  iterations_host = it;
+  B200XF_CUDA(cudaMemcpyAsync(iterations_dev, &iterations_host, sizeof(long long), cudaMemcpyHostToDevice, stream));
+  B200XF_CUDA(cudaStreamSynchronize(stream));
+  return 0;
+}
+int Context::get_iterations(long long* it) {
+  B200XF_CUDA(cudaMemcpyAsync(&iterations_host, iterations_dev, sizeof(long long), cudaMemcpyDeviceToHost, stream));
+  B200XF_CUDA(cudaStreamSynchronize(stream));
+  *it = iterations_host;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------ comm
+int Context::comm_init(const void* id128, int rank_, int world_) {
+  NcclApi* api = nccl_api();
+  if (!api) return set_error("NCCL library not found (set B200XF_NCCL_LIB)");
+  if (comm) return set_error("communicator already attached");
+  ncclUniqueId id;
+  memcpy(&id, id128, sizeof(id));
+  B200XF_CUDA(cudaSetDevice(device));
+  ncclComm_t c;
+  B200XF_NCCL(api->CommInitRank(&c, world_, id, rank_));
+  comm = c; rank = rank_; world = world_;
+  return 0;
+}
+int Context::comm_destroy() {
+  if (!comm) return 0;
+  NcclApi* api = nccl_api();
+  cudaStreamSynchronize(comm_stream);
+  if (api) api->CommDestroy(static_cast<ncclComm_t>(comm));
+  comm = nullptr; world = 1; rank = 0;
+  return 0;
+}
+int Context::allreduce(float* ptr, size_t count, cudaStream_t s) {
+  if (!comm) return set_error("no communicator attached");
+  NcclApi* api = nccl_api();
+  B200XF_NCCL(api->AllReduce(ptr, ptr, count, ncclFloat32, ncclSum, static_cast<ncclComm_t>(comm), s));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------ GEMM helpers
+int Context::dense_fwd(const bf16* x, int M, const Dense& p, bf16* y, int relu, const bf16* resid) {
+  GemmArgs g;
+  g.a = x; g.lda = p.K; g.a_mn = 0;
+  g.b = shadow + p.w; g.ldb = p.ld; g.b_mn = 1;
+  g.d = y; g.ldd = p.ld; g.d_fp32 = 0;
+  g.M = M; g.N = p.N; g.K = p.K;
+  g.bias = params + p.b; g.relu = relu;
+  g.resid = resid; g.ldr = p.ld; g.resid_op = resid ? 1 : 0;
+  return gemm_bf16(g, stream);
+}
+int Context::dense_dgrad(const bf16* dy, int M, const Dense& p, bf16* dx, const bf16* resid, int resid_op) {
+  GemmArgs g;
+  g.a = dy; g.lda = p.ld; g.a_mn = 0;
+  g.b = shadow + p.w; g.ldb = p.ld; g.b_mn = 0;  // W [K rows][N] read as [out=K][contract=N]
+  g.d = dx; g.ldd = p.K; g.d_fp32 = 0;
+  g.M = M; g.N = p.K; g.K = p.N;
+  g.resid = resid; g.ldr = p.K; g.resid_op = resid ? resid_op : 0;
+  return gemm_bf16(g, stream);
+}
+int Context::dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p) {
+  GemmArgs g;
+  g.a = x; g.lda = p.K; g.a_mn = 1;    // X [tokens][K]  == A stored [contract][M=K]
+  g.b = dy; g.ldb = p.ld; g.b_mn = 1;  // dY [tokens][N] == B stored [contract][N]
+  g.d = grads + p.w; g.ldd = p.ld; g.d_fp32 = 1; g.accumulate = 1;
+  g.M = p.K; g.N = p.N; g.K = M;
+  return gemm_bf16(g, stream);
+}
+
+// ------------------------------------------------------------------------------------ forward
+int Context::check_shapes(int B, int S, int T) {
+  if (B <= 0 || S <= 0 || T <= 0) return set_error("empty batch (B=%d S=%d T=%d)", B, S, T);
+  if (size_t(B) * S > size_t(hp.max_tokens) || size_t(B) * T > size_t(hp.max_tokens))
+    return set_error("batch of %d x %d / %d x %d tokens exceeds max_tokens=%d", B, S, B, T, hp.max_tokens);
+  if (S > hp.maximum_input_length) return set_error("input length %d exceeds maximum_input_length %d", S, hp.maximum_input_length);
+  if (T > hp.maximum_target_length) return set_error("target length %d exceeds maximum_target_length %d", T, hp.maximum_target_length);
+  return 0;
+}
+
+int Context::forward(const long long* inp, const long long* tgt_in, int B, int S, int T, float* logits_f32) {
+  B200XF_TRY(check_shapes(B, S, T));
+  const int L = hp.layers_count, d = hp.embedding_size, H = hp.heads_count, dk = d / H;
+  const int Ns = B * S, Nt = B * T;
+  const size_t cap = size_t(hp.max_tokens) * d;
+  const float eps = 1e-6f;  // transformer_model.py:187-188
+
+  // ---- encoder (transformer_model.py:270-279)
+  B200XF_TRY(embed_pe_fwd(inp, params + enc_emb, hp.input_vocabulary_size, pe_in, enc_x, B, S, d, stream));
+  for (int l = 0; l < L; ++l) {
+    const EncLayer& w = enc[l]; EncAct& a = ea[l];
+    const bf16* x = enc_x + size_t(l) * cap; bf16* out = enc_x + size_t(l + 1) * cap;
+    float* st = a.stats;
+    B200XF_TRY(dense_fwd(x, Ns, w.qkv, a.qkv, 0, nullptr));
+    AttnArgs at;
+    at.q = a.qkv; at.k = a.qkv + d; at.v = a.qkv + 2 * d; at.ldq = at.ldk = at.ldv = 3 * d;
+    at.o = a.ctx; at.ldo = d; at.lse = a.lse; at.key_tokens = inp; at.causal = 0;
+    at.B = B; at.H = H; at.Sq = S; at.Sk = S; at.dk = dk;
+    B200XF_TRY(attention_fwd(at, stream));
+    B200XF_TRY(dense_fwd(a.ctx, Ns, w.o, a.z1, 0, x));                                   // z1 = x + mha(x)
+    B200XF_TRY(layernorm_fwd(a.z1, nullptr, params + w.ln1.g, params + w.ln1.b, a.o1, nullptr, st, st + Ns, Ns, d, eps, stream));
+    B200XF_TRY(dense_fwd(a.o1, Ns, w.f1, a.h, 1, nullptr));
+    B200XF_TRY(dense_fwd(a.h, Ns, w.f2, a.z2, 0, a.o1));                                 // z2 = o1 + ffn(o1)
+    B200XF_TRY(layernorm_fwd(a.z2, nullptr, params + w.ln2.g, params + w.ln2.b, out, nullptr, st + 2 * Ns, st + 3 * Ns, Ns, d, eps, stream));
+  }
+  const bf16* enc_out = enc_x + size_t(L) * cap;
+  B200XF_TRY(dense_fwd(enc_out, Ns, kv_all, kv, 0, nullptr));  // K|V of every decoder layer's cross-attention
+
+  // ---- decoder (transformer_model.py:301-315)
+  B200XF_TRY(embed_pe_fwd(tgt_in, params + dec_emb, hp.target_vocabulary_size, pe_tgt, dec_x, B, T, d, stream));
+  for (int l = 0; l < L; ++l) {
+    const DecLayer& w = dec[l]; DecAct& a = da[l];
+    const bf16* x = dec_x + size_t(l) * cap; bf16* out = dec_x + size_t(l + 1) * cap;
+    float* st = a.stats;
+    B200XF_TRY(dense_fwd(x, Nt, w.qkv1, a.qkv, 0, nullptr));
+    AttnArgs s1;
+    s1.q = a.qkv; s1.k = a.qkv + d; s1.v = a.qkv + 2 * d; s1.ldq = s1.ldk = s1.ldv = 3 * d;
+    s1.o = a.ctx1; s1.ldo = d; s1.lse = a.lse1; s1.key_tokens = tgt_in; s1.causal = 1;
+    s1.B = B; s1.H = H; s1.Sq = T; s1.Sk = T; s1.dk = dk;
+    B200XF_TRY(attention_fwd(s1, stream));
+    B200XF_TRY(dense_fwd(a.ctx1, Nt, w.o1, a.z1, 0, x));
+    B200XF_TRY(layernorm_fwd(a.z1, nullptr, params + w.ln1.g, params + w.ln1.b, a.o1, nullptr, st, st + Nt, Nt, d, eps, stream));
+    B200XF_TRY(dense_fwd(a.o1, Nt, w.q2, a.q2, 0, nullptr));
+    AttnArgs c2;
+    c2.q = a.q2; c2.ldq = d; c2.k = kv + size_t(l) * 2 * d; c2.v = kv + size_t(l) * 2 * d + d; c2.ldk = c2.ldv = kv_all.ld;
+    c2.o = a.ctx2; c2.ldo = d; c2.lse = a.lse2; c2.key_tokens = inp; c2.causal = 0;
+    c2.B = B; c2.H = H; c2.Sq = T; c2.Sk = S; c2.dk = dk;
+    B200XF_TRY(attention_fwd(c2, stream));
+    B200XF_TRY(dense_fwd(a.ctx2, Nt, w.o2, a.z2, 0, a.o1));
+    B200XF_TRY(layernorm_fwd(a.z2, nullptr, params + w.ln2.g, params + w.ln2.b, a.o2, nullptr, st + 2 * Nt, st + 3 * Nt, Nt, d, eps, stream));
+    B200XF_TRY(dense_fwd(a.o2, Nt, w.f1, a.h, 1, nullptr));
+    B200XF_TRY(dense_fwd(a.h, Nt, w.f2, a.z3, 0, a.o2));
+    B200XF_TRY(layernorm_fwd(a.z3, nullptr, params + w.ln3.g, params + w.ln3.b, out, nullptr, st + 4 * Nt, st + 5 * Nt, Nt, d, eps, stream));
+  }
+  const bf16* dec_out = dec_x + size_t(L) * cap;
+  // ---- final_layer (transformer_model.py:347)
+  if (logits_f32) {
+    GemmArgs g;
+    g.a = dec_out; g.lda = d; g.a_mn = 0; g.b = shadow + final_layer.w; g.ldb = final_layer.ld; g.b_mn = 1;
+    g.d = logits_f32; g.ldd = final_layer.N; g.d_fp32 = 1;
+    g.M = Nt; g.N = final_layer.N; g.K = d; g.bias = params + final_layer.b;
+    B200XF_TRY(gemm_bf16(g, stream));
+  } else {
+    B200XF_TRY(dense_fwd(dec_out, Nt, final_layer, logits, 0, nullptr));
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------ backward
+int Context::ln_bwd(const bf16* dy, const bf16* z, const float* st_mean, const float* st_rstd, const LnP& p, size_t dcol_off,
+                    int rows) {
+  const int d = hp.embedding_size;
+  return layernorm_bwd(dy, z, st_mean, st_rstd, params + p.g, dz, grads + p.g, grads + p.b, grads + dcol_off, rows, d,
+                       ln_scratch, ln_counter, stream);
+}
+
+int Context::backward(const long long* inp, const long long* tgt_in, int B, int S, int T) {
+  const int L = hp.layers_count, d = hp.embedding_size, H = hp.heads_count, dk = d / H, dff = hp.feed_forward_hidden_size;
+  const int Ns = B * S, Nt = B * T;
+  const size_t cap = size_t(hp.max_tokens) * d;
+  (void)dff;
+  if (!grads_clean) B200XF_CUDA(cudaMemsetAsync(grads, 0, total_params * sizeof(float), stream));
+  grads_clean = false;
+  next_section = 0;
+
+  const bf16* dec_out = dec_x + size_t(L) * cap;
+  B200XF_TRY(dense_wgrad(dec_out, logits, Nt, final_layer));
+  B200XF_TRY(colsum_bf16(logits, final_layer.ld, Nt, final_layer.N, grads + final_layer.b, 0, stream));
+  bf16* cur = dA; bf16* other = dB;
+  B200XF_TRY(dense_dgrad(logits, Nt, final_layer, cur, nullptr, 0));
+  B200XF_TRY(section_done());
+
+  for (int l = L - 1; l >= 0; --l) {
+    const DecLayer& w = dec[l]; DecAct& a = da[l];
+    const bf16* x = dec_x + size_t(l) * cap;
+    float* st = a.stats;
+    // LN3 / FFN
+    B200XF_TRY(ln_bwd(cur, a.z3, st + 4 * Nt, st + 5 * Nt, w.ln3, w.f2.b, Nt));
+    B200XF_TRY(dense_wgrad(a.h, dz, Nt, w.f2));
+    B200XF_TRY(dense_dgrad(dz, Nt, w.f2, dh, a.h, 2));
+    B200XF_TRY(colsum_bf16(dh, w.f1.ld, Nt, w.f1.N, grads + w.f1.b, 0, stream));
+    B200XF_TRY(dense_wgrad(a.o2, dh, Nt, w.f1));
+    B200XF_TRY(dense_dgrad(dh, Nt, w.f1, other, dz, 1));
+    std::swap(cur, other);
+    // LN2 / cross attention
+    B200XF_TRY(ln_bwd(cur, a.z2, st + 2 * Nt, st + 3 * Nt, w.ln2, w.o2.b, Nt));
+    B200XF_TRY(dense_wgrad(a.ctx2, dz, Nt, w.o2));
+    B200XF_TRY(dense_dgrad(dz, Nt, w.o2, dctx, nullptr, 0));
+    AttnArgs c2;
+    c2.q = a.q2; c2.ldq = d; c2.k = kv + size_t(l) * 2 * d; c2.v = kv + size_t(l) * 2 * d + d; c2.ldk = c2.ldv = kv_all.ld;
+    c2.o = a.ctx2; c2.ldo = d; c2.lse = a.lse2; c2.key_tokens = inp; c2.causal = 0;
+    c2.B = B; c2.H = H; c2.Sq = T; c2.Sk = S; c2.dk = dk;
+    c2.d_o = dctx; c2.lddo = d; c2.dq = dq2; c2.lddq = d;
+    c2.dk_out = dkv + size_t(l) * 2 * d; c2.dv_out = dkv + size_t(l) * 2 * d + d; c2.lddk = c2.lddv = kv_all.ld; c2.delta = delta;
+    B200XF_TRY(attention_bwd(c2, stream));
+    B200XF_TRY(colsum_bf16(dq2, d, Nt, d, grads + w.q2.b, 0, stream));
+    B200XF_TRY(dense_wgrad(a.o1, dq2, Nt, w.q2));
+    B200XF_TRY(dense_dgrad(dq2, Nt, w.q2, other, dz, 1));
+    std::swap(cur, other);
+    // LN1 / causal self attention
+    B200XF_TRY(ln_bwd(cur, a.z1, st, st + Nt, w.ln1, w.o1.b, Nt));
+    B200XF_TRY(dense_wgrad(a.ctx1, dz, Nt, w.o1));
+    B200XF_TRY(dense_dgrad(dz, Nt, w.o1, dctx, nullptr, 0));
+    AttnArgs s1;
+    s1.q = a.qkv; s1.k = a.qkv + d; s1.v = a.qkv + 2 * d; s1.ldq = s1.ldk = s1.ldv = 3 * d;
+    s1.o = a.ctx1; s1.ldo = d; s1.lse = a.lse1; s1.key_tokens = tgt_in; s1.causal = 1;
+    s1.B = B; s1.H = H; s1.Sq = T; s1.Sk = T; s1.dk = dk;
+    s1.d_o = dctx; s1.lddo = d; s1.dq = dqkv; s1.dk_out = dqkv + d; s1.dv_out = dqkv + 2 * d; s1.lddq = s1.lddk = s1.lddv = 3 * d;
+    s1.delta = delta;
+    B200XF_TRY(attention_bwd(s1, stream));
+    B200XF_TRY(colsum_bf16(dqkv, 3 * d, Nt, 3 * d, grads + w.qkv1.b, 0, stream));
+    B200XF_TRY(dense_wgrad(x, dqkv, Nt, w.qkv1));
+    B200XF_TRY(dense_dgrad(dqkv, Nt, w.qkv1, other, dz, 1));
+    std::swap(cur, other);
+    B200XF_TRY(section_done());
+  }
+  B200XF_TRY(embed_bwd(tgt_in, cur, grads + dec_emb, hp.target_vocabulary_size, Nt, d, emb_scratch, emb_scratch_bytes, stream));
+  const bf16* enc_out = enc_x + size_t(L) * cap;
+  B200XF_TRY(colsum_bf16(dkv, kv_all.ld, Ns, kv_all.N, grads + kv_all.b, 0, stream));
+  B200XF_TRY(dense_wgrad(enc_out, dkv, Ns, kv_all));
+  B200XF_TRY(dense_dgrad(dkv, Ns, kv_all, cur, nullptr, 0));
+  B200XF_TRY(section_done());
+
+  for (int l = L - 1; l >= 0; --l) {
+    const EncLayer& w = enc[l]; EncAct& a = ea[l];
+    const bf16* x = enc_x + size_t(l) * cap;
+    float* st = a.stats;
+    B200XF_TRY(ln_bwd(cur, a.z2, st + 2 * Ns, st + 3 * Ns, w.ln2, w.f2.b, Ns));
+    B200XF_TRY(dense_wgrad(a.h, dz, Ns, w.f2));
+    B200XF_TRY(dense_dgrad(dz, Ns, w.f2, dh, a.h, 2));
+    B200XF_TRY(colsum_bf16(dh, w.f1.ld, Ns, w.f1.N, grads + w.f1.b, 0, stream));
+    B200XF_TRY(dense_wgrad(a.o1, dh, Ns, w.f1));
+    B200XF_TRY(dense_dgrad(dh, Ns, w.f1, other, dz, 1));
+    std::swap(cur, other);
+    B200XF_TRY(ln_bwd(cur, a.z1, st, st + Ns, w.ln1, w.o.b, Ns));
+    B200XF_TRY(dense_wgrad(a.ctx, dz, Ns, w.o));
+    B200XF_TRY(dense_dgrad(dz, Ns, w.o, dctx, nullptr, 0));
+    AttnArgs at;
+    at.q = a.qkv; at.k = a.qkv + d; at.v = a.qkv + 2 * d; at.ldq = at.ldk = at.ldv = 3 * d;
+    at.o = a.ctx; at.ldo = d; at.lse = a.lse; at.key_tokens = inp; at.causal = 0;
+    at.B = B; at.H = H; at.Sq = S; at.Sk = S; at.dk = dk;
+    at.d_o = dctx; at.lddo = d; at.dq = dqkv; at.dk_out = dqkv + d; at.dv_out = dqkv + 2 * d; at.lddq = at.lddk = at.lddv = 3 * d;
+    at.delta = delta;
+    B200XF_TRY(attention_bwd(at, stream));
+    B200XF_TRY(colsum_bf16(dqkv, 3 * d, Ns, 3 * d, grads + w.qkv.b, 0, stream));
+    B200XF_TRY(dense_wgrad(x, dqkv, Ns, w.qkv));
+    B200XF_TRY(dense_dgrad(dqkv, Ns, w.qkv, other, dz, 1));
+    std::swap(cur, other);
+    B200XF_TRY(section_done());
+  }
+  B200XF_TRY(embed_bwd(inp, cur, grads + enc_emb, hp.input_vocabulary_size, Ns, d, emb_scratch, emb_scratch_bytes, stream));
+  B200XF_TRY(section_done());
+  return 0;
+}
+
+// Called each time backward finishes one layout section.  With a communicator attached and updates enabled,
+// completed sections are grouped into buckets of >= bucket_bytes; each bucket is all-reduced on the comm
+// stream (after an event on the compute stream) and its Adam update is chained behind the reduce, so both
+// hide under the remaining backward.  Without a communicator nothing happens here (one Adam at the end).
+int Context::section_done() {
+  const size_t idx = next_section++;
+  if (!overlap_update || !comm) return 0;
+  const size_t end = sections[idx].second;
+  const bool last = (idx + 1 == sections.size());
+  if (!last && (end - bucket_begin) * sizeof(float) < bucket_bytes) return 0;
+  B200XF_CUDA(cudaEventRecord(ev_ready, stream));
+  B200XF_CUDA(cudaStreamWaitEvent(comm_stream, ev_ready, 0));
+  B200XF_TRY(allreduce(grads + bucket_begin, end - bucket_begin, comm_stream));
+  B200XF_TRY(adam_step(params + bucket_begin, grads + bucket_begin, adam_m + bucket_begin, adam_v + bucket_begin,
+                       shadow + bucket_begin, end - bucket_begin, iterations_dev, adam, 1, comm_stream));
+  bucket_begin = end;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------ steps
+int Context::loss_and_grad(int Nt, int workers_count, int write_grad) {
+  const float inv_w = 1.0f / float(workers_count);
+  B200XF_TRY(vocab_ce_fwd_bwd(logits, final_layer.ld, tok_labels, Nt, final_layer.N, nonpad_count, inv_w, row_loss, row_correct,
+                              write_grad, stream));
+  B200XF_TRY(ce_finalize(row_loss, row_correct, nonpad_count, Nt, inv_w, metrics, stream));
+  return 0;
+}
+
+int Context::step_device(const long long* inp, const long long* target, int B, int S, int T1, int workers_count, int mode,
+                         float* out6) {
+  // mode 0: eval (fwd + loss), 1: fwd + bwd, 2: full train step
+  if (T1 < 2) return set_error("target needs at least 2 positions");
+  const int T = T1 - 1;
+  B200XF_TRY(check_shapes(B, S, T));
+  if (workers_count <= 0) return set_error("workers_count must be positive");
+  B200XF_CUDA(cudaSetDevice(device));
+  B200XF_TRY(prep_targets(target, tok_tgt_in, tok_labels, nonpad_count, B, T1, stream));
+  B200XF_TRY(forward(inp, tok_tgt_in, B, S, T, nullptr));
+  B200XF_TRY(loss_and_grad(B * T, workers_count, mode != 0));
+  if (mode >= 1) {
+    overlap_update = (mode == 2) && comm != nullptr;
+    bucket_begin = 0;
+    B200XF_TRY(backward(inp, tok_tgt_in, B, S, T));
+  }
+  if (mode == 2) {
+    if (comm) {
+      // metrics: local values stay in metrics[0..2]; reduced copy in metrics[3..5]
+      B200XF_CUDA(cudaMemcpyAsync(metrics + 3, metrics, 3 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+      B200XF_CUDA(cudaEventRecord(ev_ready, stream));
+      B200XF_CUDA(cudaStreamWaitEvent(comm_stream, ev_ready, 0));
+      B200XF_TRY(allreduce(metrics + 3, 3, comm_stream));
+      B200XF_CUDA(cudaEventRecord(ev_done, comm_stream));
+      B200XF_CUDA(cudaStreamWaitEvent(stream, ev_done, 0));  // weights + metrics ready for whatever follows
+      grads_clean = true;
+    } else {
+      B200XF_CUDA(cudaMemcpyAsync(metrics + 3, metrics, 3 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+      B200XF_TRY(adam_step(params, grads, adam_m, adam_v, shadow, total_params, iterations_dev, adam, 1, stream));
+      grads_clean = true;
+    }
+    B200XF_TRY(increment_counter(iterations_dev, stream));
+  } else {
+    B200XF_CUDA(cudaMemcpyAsync(metrics + 3, metrics, 3 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  }
+  if (out6) B200XF_CUDA(cudaMemcpyAsync(out6, metrics, 6 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  return 0;
+}
+
+int Context::step_host(const long long* inp, const long long* target, int B, int S, int T1, int workers_count, float* out6_host) {
+  if (T1 < 2) return set_error("target needs at least 2 positions");
+  B200XF_TRY(check_shapes(B, S, T1 - 1));
+  B200XF_CUDA(cudaSetDevice(device));
+  B200XF_CUDA(cudaMemcpyAsync(tok_inp, inp, size_t(B) * S * sizeof(long long), cudaMemcpyHostToDevice, stream));
+  B200XF_CUDA(cudaMemcpyAsync(tok_target, target, size_t(B) * T1 * sizeof(long long), cudaMemcpyHostToDevice, stream));
+  B200XF_TRY(step_device(tok_inp, tok_target, B, S, T1, workers_count, 2, nullptr));
+  B200XF_CUDA(cudaMemcpyAsync(host_out, metrics, 6 * sizeof(float), cudaMemcpyDeviceToHost, stream));
+  B200XF_CUDA(cudaStreamSynchronize(stream));
+  memcpy(out6_host, host_out, 6 * sizeof(float));
+  return 0;
+}
+
+}  // namespace b200xf

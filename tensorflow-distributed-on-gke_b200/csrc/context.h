@@ -1,0 +1,94 @@
+// Context: parameters, optimizer state, activations/workspace and the step orchestration.
+#pragma once
+#include <map>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/b200xf.h"
+#include "internal.h"
+
+namespace b200xf {
+
+struct Dense { size_t w = 0, b = 0; int K = 0, N = 0, ld = 0; };  // kernel [K, N] (row pitch ld), bias [N]
+struct LnP { size_t g = 0, b = 0; };
+struct EncLayer { Dense qkv, o, f1, f2; LnP ln1, ln2; };
+struct DecLayer { Dense qkv1, o1, q2, o2, f1, f2; LnP ln1, ln2, ln3; };
+struct ParamView { std::string name; int64_t rows, cols, ld, offset; int ndim; };
+
+struct EncAct { bf16 *qkv, *ctx, *z1, *o1, *h, *z2; float *lse, *stats; };
+struct DecAct { bf16 *qkv, *ctx1, *z1, *o1, *q2, *ctx2, *z2, *o2, *z3, *h; float *lse1, *lse2, *stats; };
+
+int comm_unique_id(void* out128);
+void positional_encoding_host(float* out, int positions, int d);
+
+struct Context {
+  b200xf_hparams hp{};
+  int device = 0;
+  cudaStream_t stream = nullptr;
+
+  // ---- parameters (flat) and their logical views
+  size_t total_params = 0;
+  int vt_ld = 0;
+  Dense final_layer, kv_all;
+  size_t enc_emb = 0, dec_emb = 0;
+  std::vector<EncLayer> enc;
+  std::vector<DecLayer> dec;
+  std::map<std::string, ParamView> views;
+  std::vector<ParamView> table;
+  std::vector<std::pair<size_t, size_t>> sections;  // [begin, end) ranges in backward completion order
+  float *params = nullptr, *grads = nullptr, *adam_m = nullptr, *adam_v = nullptr;
+  bf16* shadow = nullptr;
+  bool grads_clean = true;
+  AdamHyper adam{};
+  long long* iterations_dev = nullptr;
+  long long iterations_host = 0;
+
+  // ---- workspace
+  char* arena = nullptr; size_t arena_size = 0, arena_used = 0;
+  bf16 *enc_x = nullptr, *dec_x = nullptr, *kv = nullptr, *dkv = nullptr, *logits = nullptr;
+  std::vector<EncAct> ea; std::vector<DecAct> da;
+  bf16 *dA = nullptr, *dB = nullptr, *dz = nullptr, *dctx = nullptr, *dq2 = nullptr, *dh = nullptr, *dqkv = nullptr;
+  float *delta = nullptr, *row_loss = nullptr, *ln_scratch = nullptr, *pe_in = nullptr, *pe_tgt = nullptr, *metrics = nullptr;
+  int *row_correct = nullptr, *nonpad_count = nullptr;
+  unsigned* ln_counter = nullptr;
+  long long *tok_inp = nullptr, *tok_target = nullptr, *tok_tgt_in = nullptr, *tok_labels = nullptr;
+  char* emb_scratch = nullptr; size_t emb_scratch_bytes = 0;
+  float* host_out = nullptr;
+
+  // ---- data parallel
+  void* comm = nullptr; int rank = 0, world = 1;
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
+  size_t bucket_bytes = size_t(32) << 20, bucket_begin = 0, next_section = 0;
+  bool overlap_update = false;
+
+  ~Context();
+  int init(const b200xf_hparams& h, int dev, cudaStream_t s);
+  void build_layout();
+  size_t add_tensor(size_t& cursor, size_t elems);
+  Dense add_dense(size_t& cursor, int K, int N, int ld);
+  void add_view(const std::string& name, size_t offset, int64_t rows, int64_t cols, int64_t ld, int ndim);
+  template <typename T> int arena_alloc(T** out, size_t count);
+
+  int params_changed();
+  int set_iterations(long long it);
+  int get_iterations(long long* it);
+  int comm_init(const void* id128, int rank, int world);
+  int comm_destroy();
+  int allreduce(float* ptr, size_t count, cudaStream_t s);
+
+  int dense_fwd(const bf16* x, int M, const Dense& p, bf16* y, int relu, const bf16* resid);
+  int dense_dgrad(const bf16* dy, int M, const Dense& p, bf16* dx, const bf16* resid, int resid_op);
+  int dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p);
+  int ln_bwd(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const LnP& p, size_t dcol_off, int rows);
+  int check_shapes(int B, int S, int T);
+  int forward(const long long* inp, const long long* tgt_in, int B, int S, int T, float* logits_f32);
+  int backward(const long long* inp, const long long* tgt_in, int B, int S, int T);
+  int section_done();
+  int loss_and_grad(int Nt, int workers_count, int write_grad);
+  int step_device(const long long* inp, const long long* target, int B, int S, int T1, int workers_count, int mode, float* out6);
+  int step_host(const long long* inp, const long long* target, int B, int S, int T1, int workers_count, float* out6_host);
+};
+
+}  // namespace b200xf

@@ -1,0 +1,616 @@
+// HBM-bound kernels of the train step: LayerNorm (+residual) fwd/bwd, embedding*sqrt(d)+PE fwd/bwd,
+// target shift + PAD count, masked softmax cross-entropy over the vocab (fwd+bwd fused), Adam with
+// the warm-up schedule over flat buckets, column sums (bias gradients), casts.
+// All global accesses are 128-bit vectorised and coalesced; reductions use warp shuffles.
+#include <algorithm>
+#include <cub/device/device_radix_sort.cuh>
+
+#include "internal.h"
+#include "ptx.cuh"
+
+namespace b200xf {
+
+namespace {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ void unpack8(const uint4& u, float* f) {
+  f[0] = ptx::bf16_lo(u.x); f[1] = ptx::bf16_hi(u.x); f[2] = ptx::bf16_lo(u.y); f[3] = ptx::bf16_hi(u.y);
+  f[4] = ptx::bf16_lo(u.z); f[5] = ptx::bf16_hi(u.z); f[6] = ptx::bf16_lo(u.w); f[7] = ptx::bf16_hi(u.w);
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 u;
+  u.x = ptx::pack_bf16x2(f[0], f[1]); u.y = ptx::pack_bf16x2(f[2], f[3]);
+  u.z = ptx::pack_bf16x2(f[4], f[5]); u.w = ptx::pack_bf16x2(f[6], f[7]);
+  return u;
+}
+__device__ __forceinline__ float round_bf16(float x) { return __bfloat162float(__float2bfloat16(x)); }
+
+// ============================================================================ LayerNorm
+// One warp per row; the row lives in registers (CH chunks of 8 bf16 per lane): one HBM read, one write.
+constexpr int kLnWarps = 8;
+
+template <int CH>
+__global__ void __launch_bounds__(kLnWarps * 32)
+ln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ resid, const float* __restrict__ gamma,
+              const float* __restrict__ beta, bf16* __restrict__ y, bf16* __restrict__ z_out, float* __restrict__ mean_out,
+              float* __restrict__ rstd_out, int rows, int d, float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * kLnWarps + warp;
+  if (row >= rows) return;
+  const size_t base = size_t(row) * d;
+  float v[CH][8];
+  float sum = 0.f;
+#pragma unroll
+  for (int c = 0; c < CH; ++c) {
+    const int col = (c * 32 + lane) * 8;
+    if (col < d) {
+      unpack8(*reinterpret_cast<const uint4*>(x + base + col), v[c]);
+      if (resid) {
+        float r[8];
+        unpack8(*reinterpret_cast<const uint4*>(resid + base + col), r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[c][j] = round_bf16(v[c][j] + r[j]);  // z is kept in bf16 for the backward
+        if (z_out) *reinterpret_cast<uint4*>(z_out + base + col) = pack8(v[c]);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sum += v[c][j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[c][j] = 0.f;
+    }
+  }
+  const float mean = warp_sum(sum) / float(d);
+  float sq = 0.f;
+#pragma unroll
+  for (int c = 0; c < CH; ++c) {
+    const int col = (c * 32 + lane) * 8;
+    if (col < d) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { const float t = v[c][j] - mean; sq += t * t; }
+    }
+  }
+  const float var = warp_sum(sq) / float(d);  // biased variance, as tf.nn.moments
+  const float rstd = 1.0f / sqrtf(var + eps);
+#pragma unroll
+  for (int c = 0; c < CH; ++c) {
+    const int col = (c * 32 + lane) * 8;
+    if (col < d) {
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + col)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + col + 4));
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + col)), b1 = __ldg(reinterpret_cast<const float4*>(beta + col + 4));
+      const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+      const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = (v[c][j] - mean) * rstd * g[j] + b[j];
+      *reinterpret_cast<uint4*>(y + base + col) = pack8(o);
+    }
+  }
+  if (lane == 0) { mean_out[row] = mean; rstd_out[row] = rstd; }
+}
+
+// Backward: dz = rstd * (g - mean(g) - xhat * mean(g*xhat)),  g = dy * gamma.
+// Column sums (dgamma, dbeta, colsum(dz)) are accumulated per lane across the block's rows, reduced
+// across the block's warps in shared memory in a fixed order, written as per-block partials, and summed
+// by the last block to finish (threadfence + counter) — deterministic, no float atomics.
+template <int CH>
+__global__ void __launch_bounds__(kLnWarps * 32)
+ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const float* __restrict__ mean_in,
+              const float* __restrict__ rstd_in, const float* __restrict__ gamma, bf16* __restrict__ dz,
+              float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dcol, int rows, int d,
+              float* __restrict__ scratch, unsigned* __restrict__ counter) {
+  extern __shared__ float red[];  // [3][d]
+  __shared__ bool is_last;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float gam[CH][8];
+  float acc_g[CH][8], acc_b[CH][8], acc_c[CH][8];
+#pragma unroll
+  for (int c = 0; c < CH; ++c) {
+    const int col = (c * 32 + lane) * 8;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { acc_g[c][j] = acc_b[c][j] = acc_c[c][j] = 0.f; gam[c][j] = (col < d) ? __ldg(gamma + col + j) : 0.f; }
+  }
+  for (int row = blockIdx.x * kLnWarps + warp; row < rows; row += gridDim.x * kLnWarps) {
+    const size_t base = size_t(row) * d;
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float xh[CH][8], g[CH][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+      const int col = (c * 32 + lane) * 8;
+      if (col < d) {
+        float a[8], b[8];
+        unpack8(*reinterpret_cast<const uint4*>(dy + base + col), a);
+        unpack8(*reinterpret_cast<const uint4*>(z + base + col), b);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[c][j] = (b[j] - mean) * rstd;
+          g[c][j] = a[j] * gam[c][j];
+          s1 += g[c][j]; s2 += g[c][j] * xh[c][j];
+          acc_g[c][j] += a[j] * xh[c][j];
+          acc_b[c][j] += a[j];
+        }
+      }
+    }
+    const float m1 = warp_sum(s1) / float(d), m2 = warp_sum(s2) / float(d);
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+      const int col = (c * 32 + lane) * 8;
+      if (col < d) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { o[j] = rstd * (g[c][j] - m1 - xh[c][j] * m2); acc_c[c][j] += round_bf16(o[j]); }
+        *reinterpret_cast<uint4*>(dz + base + col) = pack8(o);
+      }
+    }
+  }
+  // block reduce: warps add into shared memory one after another (fixed order)
+  for (int i = threadIdx.x; i < 3 * d; i += blockDim.x) red[i] = 0.f;
+  __syncthreads();
+  for (int w = 0; w < kLnWarps; ++w) {
+    if (warp == w) {
+#pragma unroll
+      for (int c = 0; c < CH; ++c) {
+        const int col = (c * 32 + lane) * 8;
+        if (col < d) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) { red[col + j] += acc_g[c][j]; red[d + col + j] += acc_b[c][j]; red[2 * d + col + j] += acc_c[c][j]; }
+        }
+      }
+    }
+    __syncthreads();
+  }
+  float* mine = scratch + size_t(blockIdx.x) * 3 * d;
+  for (int i = threadIdx.x; i < 3 * d; i += blockDim.x) mine[i] = red[i];
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  for (int i = threadIdx.x; i < 3 * d; i += blockDim.x) {
+    float s = 0.f;
+    for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(scratch + size_t(b) * 3 * d + i);
+    if (i < d) dgamma[i] = s;
+    else if (i < 2 * d) dbeta[i - d] = s;
+    else if (dcol) dcol[i - 2 * d] = s;
+  }
+  if (threadIdx.x == 0) *counter = 0u;  // leave the counter ready for the next call
+}
+
+int ln_bwd_grid(int rows) { return max(1, min((rows + kLnWarps - 1) / kLnWarps, 2 * num_sms())); }
+
+}  // namespace
+
+int layernorm_fwd(const bf16* x, const bf16* resid, const float* gamma, const float* beta, bf16* y, bf16* z_out, float* mean,
+                  float* rstd, int rows, int d, float eps, cudaStream_t stream) {
+  if (d % 8 || d > 2048) return set_error("layernorm: d=%d must be a multiple of 8 and <= 2048", d);
+  if (rows <= 0) return 0;
+  const int grid = (rows + kLnWarps - 1) / kLnWarps;
+  const int ch = (d + 255) / 256;
+#define LN_FWD(CH) ln_fwd_kernel<CH><<<grid, kLnWarps * 32, 0, stream>>>(x, resid, gamma, beta, y, z_out, mean, rstd, rows, d, eps)
+  if (ch <= 1) LN_FWD(1); else if (ch <= 2) LN_FWD(2); else if (ch <= 4) LN_FWD(4); else LN_FWD(8);
+#undef LN_FWD
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+size_t ln_bwd_scratch_floats(int rows, int d) { return size_t(ln_bwd_grid(rows)) * 3 * d; }
+
+int layernorm_bwd(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const float* gamma, bf16* dz,
+                  float* dgamma, float* dbeta, float* dcol, int rows, int d, float* scratch, unsigned* counter,
+                  cudaStream_t stream) {
+  if (d % 8 || d > 2048) return set_error("layernorm: d=%d must be a multiple of 8 and <= 2048", d);
+  if (rows <= 0) return 0;
+  const int grid = ln_bwd_grid(rows);
+  const int ch = (d + 255) / 256;
+  const size_t smem = size_t(3) * d * sizeof(float);
+#define LN_BWD(CH) ln_bwd_kernel<CH><<<grid, kLnWarps * 32, smem, stream>>>(dy, z, mean, rstd, gamma, dz, dgamma, dbeta, dcol, rows, d, scratch, counter)
+  if (ch <= 1) LN_BWD(1); else if (ch <= 2) LN_BWD(2); else if (ch <= 4) LN_BWD(4); else LN_BWD(8);
+#undef LN_BWD
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+// ============================================================================ embedding + PE
+namespace {
+
+// x[b,s,:] = table[token] * sqrt(d) + pe[s]   (fp32 master rows gathered bit-exactly, output bf16)
+__global__ void embed_fwd_kernel(const long long* __restrict__ tokens, const float* __restrict__ table, int vocab,
+                                 const float* __restrict__ pe, bf16* __restrict__ out, int S, int d, float scale) {
+  const int n = blockIdx.x;
+  const long long tok = tokens[n];
+  const bool ok = tok >= 0 && tok < vocab;  // out-of-range ids read as a zero row (TF GPU gather semantics)
+  const float* row = table + size_t(ok ? tok : 0) * d;
+  const float* p = pe + size_t(n % S) * d;
+  for (int c = threadIdx.x * 4; c < d; c += blockDim.x * 4) {
+    float4 e = ok ? __ldg(reinterpret_cast<const float4*>(row + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 q = __ldg(reinterpret_cast<const float4*>(p + c));
+    uint2 u;
+    u.x = ptx::pack_bf16x2(e.x * scale + q.x, e.y * scale + q.y);
+    u.y = ptx::pack_bf16x2(e.z * scale + q.z, e.w * scale + q.w);
+    *reinterpret_cast<uint2*>(out + size_t(n) * d + c) = u;
+  }
+}
+
+__global__ void embed_keys_kernel(const long long* __restrict__ tokens, int* __restrict__ keys, int* __restrict__ vals, int n, int vocab) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const long long t = tokens[i];
+  keys[i] = (t >= 0 && t < vocab) ? int(t) : vocab;  // out-of-range ids sort last and are skipped
+  vals[i] = i;
+}
+
+// One block per sorted position; the block at the head of a run of equal token ids sums that run's
+// gradient rows in sorted (= original position) order and writes the table row once: deterministic.
+__global__ void embed_bwd_kernel(const int* __restrict__ keys, const int* __restrict__ vals, const bf16* __restrict__ dx,
+                                 float* __restrict__ dtable, int n, int d, int vocab, float scale) {
+  const int p = blockIdx.x;
+  const int key = keys[p];
+  if (key >= vocab || (p > 0 && keys[p - 1] == key)) return;
+  int end = p + 1;
+  while (end < n && keys[end] == key) ++end;
+  for (int c = threadIdx.x * 4; c < d; c += blockDim.x * 4) {
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    for (int q = p; q < end; ++q) {
+      const uint2 u = *reinterpret_cast<const uint2*>(dx + size_t(vals[q]) * d + c);
+      a0 += ptx::bf16_lo(u.x); a1 += ptx::bf16_hi(u.x); a2 += ptx::bf16_lo(u.y); a3 += ptx::bf16_hi(u.y);
+    }
+    float4* dst = reinterpret_cast<float4*>(dtable + size_t(key) * d + c);
+    float4 cur = *dst;
+    cur.x += a0 * scale; cur.y += a1 * scale; cur.z += a2 * scale; cur.w += a3 * scale;
+    *dst = cur;
+  }
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+int embed_pe_fwd(const long long* tokens, const float* table, int vocab, const float* pe, bf16* out, int B, int S, int d,
+                 cudaStream_t stream) {
+  if (d % 4) return set_error("embedding: d=%d must be a multiple of 4", d);
+  const int n = B * S;
+  if (n <= 0) return 0;
+  const int threads = min(256, max(32, (d / 4 + 31) / 32 * 32));
+  embed_fwd_kernel<<<n, threads, 0, stream>>>(tokens, table, vocab, pe, out, S, d, sqrtf(float(d)));
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+size_t embed_bwd_scratch_bytes(int n) {
+  size_t temp = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, temp, (const int*)nullptr, (int*)nullptr, (const int*)nullptr, (int*)nullptr, n);
+  return align_up(temp, 256) + 4 * align_up(size_t(n) * sizeof(int), 256);
+}
+
+int embed_bwd(const long long* tokens, const bf16* dx, float* dtable, int vocab, int n, int d, void* scratch, size_t scratch_bytes,
+              cudaStream_t stream) {
+  if (n <= 0) return 0;
+  if (scratch_bytes < embed_bwd_scratch_bytes(n)) return set_error("embed_bwd: scratch too small");
+  const size_t seg = align_up(size_t(n) * sizeof(int), 256);
+  char* base = static_cast<char*>(scratch);
+  int* keys_in = reinterpret_cast<int*>(base);
+  int* keys_out = reinterpret_cast<int*>(base + seg);
+  int* vals_in = reinterpret_cast<int*>(base + 2 * seg);
+  int* vals_out = reinterpret_cast<int*>(base + 3 * seg);
+  void* temp = base + 4 * seg;
+  size_t temp_bytes = scratch_bytes - 4 * seg;
+  embed_keys_kernel<<<(n + 255) / 256, 256, 0, stream>>>(tokens, keys_in, vals_in, n, vocab);
+  int bits = 1;
+  while ((1ll << bits) <= vocab) ++bits;
+  B200XF_CUDA(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, n, 0, bits, stream));
+  const int threads = min(256, max(32, (d / 4 + 31) / 32 * 32));
+  embed_bwd_kernel<<<n, threads, 0, stream>>>(keys_out, vals_out, dx, dtable, n, d, vocab, sqrtf(float(d)));
+  B200XF_CUDA(cudaGetLastError());
+  count_launch(3);
+  return 0;
+}
+
+// ============================================================================ targets
+namespace {
+__global__ void prep_targets_kernel(const long long* __restrict__ target, long long* __restrict__ tgt_in,
+                                    long long* __restrict__ labels, int* __restrict__ count, int B, int T1) {
+  __shared__ int warp_cnt[32];
+  const int T = T1 - 1;
+  int local = 0;
+  for (int i = threadIdx.x; i < B * T; i += blockDim.x) {
+    const int b = i / T, t = i % T;
+    const long long a = target[size_t(b) * T1 + t], l = target[size_t(b) * T1 + t + 1];
+    tgt_in[i] = a; labels[i] = l;
+    local += (l != 0);
+  }
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  if ((threadIdx.x & 31) == 0) warp_cnt[threadIdx.x >> 5] = local;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int s = 0;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) s += warp_cnt[w];
+    *count = s;
+  }
+}
+}  // namespace
+
+int prep_targets(const long long* target, long long* tgt_in, long long* labels, int* nonpad_count, int B, int T_plus_1,
+                 cudaStream_t stream) {
+  if (T_plus_1 < 2) return set_error("target must have at least 2 positions");
+  prep_targets_kernel<<<1, 1024, 0, stream>>>(target, tgt_in, labels, nonpad_count, B, T_plus_1);
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+// ============================================================================ softmax cross-entropy
+namespace {
+constexpr int kCeThreads = 256;
+
+struct MaxSum { float m, s; };
+__device__ __forceinline__ MaxSum combine(MaxSum a, MaxSum b) {
+  const float m = fmaxf(a.m, b.m);
+  if (m == -INFINITY) return {m, 0.f};
+  return {m, a.s * exp2f((a.m - m) * 1.4426950408889634f) + b.s * exp2f((b.m - m) * 1.4426950408889634f)};
+}
+
+// One block per target position: pass 1 = online max/sum-exp, first-max argmax, label logit;
+// pass 2 (row now L2-resident) = dlogits = (softmax - onehot) * mask / (count * workers), in place.
+__global__ void __launch_bounds__(kCeThreads)
+vocab_ce_kernel(bf16* __restrict__ logits, int ldl, const long long* __restrict__ labels, int V,
+                const int* __restrict__ nonpad_count, float inv_workers, float* __restrict__ row_loss,
+                int* __restrict__ row_correct, int write_grad) {
+  __shared__ float sm_m[kCeThreads / 32], sm_s[kCeThreads / 32], sm_am[kCeThreads / 32];
+  __shared__ int sm_ai[kCeThreads / 32];
+  __shared__ float bc[3];
+  __shared__ int bci;
+  const int row = blockIdx.x;
+  bf16* x = logits + size_t(row) * ldl;
+  const long long label = labels[row];
+  const int nvec = (V + 7) / 8;
+  if (label == 0) {  // PAD target: contributes nothing (transformer_model.py:12-15)
+    if (write_grad)
+      for (int i = threadIdx.x; i < nvec; i += kCeThreads) {
+        if (i * 8 + 8 <= V) *reinterpret_cast<uint4*>(x + i * 8) = make_uint4(0, 0, 0, 0);
+        else for (int j = i * 8; j < V; ++j) x[j] = __float2bfloat16(0.f);
+      }
+    if (threadIdx.x == 0) { row_loss[row] = 0.f; row_correct[row] = 0; }
+    return;
+  }
+  MaxSum ms{-INFINITY, 0.f};
+  float am = -INFINITY; int ai = 0x7fffffff;
+  for (int i = threadIdx.x; i < nvec; i += kCeThreads) {
+    float f[8];
+    if (i * 8 + 8 <= V) unpack8(*reinterpret_cast<const uint4*>(x + i * 8), f);
+    else for (int j = 0; j < 8; ++j) f[j] = (i * 8 + j < V) ? __bfloat162float(x[i * 8 + j]) : -INFINITY;
+    float lm = f[0];
+#pragma unroll
+    for (int j = 1; j < 8; ++j) lm = fmaxf(lm, f[j]);
+    if (lm > am) {  // strictly greater keeps the earliest index within this thread's ascending scan
+#pragma unroll
+      for (int j = 7; j >= 0; --j) if (f[j] == lm) ai = i * 8 + j;
+      am = lm;
+    }
+    float ls = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) ls += exp2f((f[j] - lm) * 1.4426950408889634f);
+    ms = combine(ms, MaxSum{lm, ls});
+  }
+  // warp then block reduction
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    MaxSum other{__shfl_xor_sync(0xffffffffu, ms.m, o), __shfl_xor_sync(0xffffffffu, ms.s, o)};
+    ms = combine(ms, other);
+    const float om = __shfl_xor_sync(0xffffffffu, am, o); const int oi = __shfl_xor_sync(0xffffffffu, ai, o);
+    if (om > am || (om == am && oi < ai)) { am = om; ai = oi; }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) { sm_m[warp] = ms.m; sm_s[warp] = ms.s; sm_am[warp] = am; sm_ai[warp] = ai; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    MaxSum t{sm_m[0], sm_s[0]}; float bm = sm_am[0]; int bi = sm_ai[0];
+    for (int w = 1; w < kCeThreads / 32; ++w) {
+      t = combine(t, MaxSum{sm_m[w], sm_s[w]});
+      if (sm_am[w] > bm || (sm_am[w] == bm && sm_ai[w] < bi)) { bm = sm_am[w]; bi = sm_ai[w]; }
+    }
+    const bool label_ok = label > 0 && label < V;
+    const float xl = label_ok ? __bfloat162float(x[label]) : 0.f;
+    const float lse = t.m + logf(t.s);
+    row_loss[row] = lse - xl;
+    row_correct[row] = (bi == int(label)) ? 1 : 0;
+    bc[0] = t.m; bc[1] = 1.0f / t.s;
+    bc[2] = inv_workers / float(max(*nonpad_count, 1));
+    bci = label_ok ? int(label) : -1;
+  }
+  if (!write_grad) return;
+  __syncthreads();
+  const float mx = bc[0], inv_s = bc[1], scale = bc[2];
+  const int lab = bci;
+  for (int i = threadIdx.x; i < nvec; i += kCeThreads) {
+    float f[8];
+    const bool fullv = i * 8 + 8 <= V;
+    if (fullv) unpack8(*reinterpret_cast<const uint4*>(x + i * 8), f);
+    else for (int j = 0; j < 8; ++j) f[j] = (i * 8 + j < V) ? __bfloat162float(x[i * 8 + j]) : -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float pr = exp2f((f[j] - mx) * 1.4426950408889634f) * inv_s;
+      f[j] = (pr - ((i * 8 + j == lab) ? 1.f : 0.f)) * scale;
+    }
+    if (fullv) *reinterpret_cast<uint4*>(x + i * 8) = pack8(f);
+    else for (int j = 0; j < 8; ++j) if (i * 8 + j < V) x[i * 8 + j] = __float2bfloat16(f[j]);
+  }
+}
+
+__global__ void ce_finalize_kernel(const float* __restrict__ row_loss, const int* __restrict__ row_correct,
+                                   const int* __restrict__ nonpad_count, int rows, float inv_workers, float* __restrict__ out3) {
+  __shared__ float wl[32]; __shared__ int wc[32];
+  float l = 0.f; int c = 0;
+  // fixed assignment of rows to threads and a fixed reduction tree: deterministic
+  for (int i = threadIdx.x; i < rows; i += blockDim.x) { l += row_loss[i]; c += row_correct[i]; }
+  for (int o = 16; o > 0; o >>= 1) { l += __shfl_xor_sync(0xffffffffu, l, o); c += __shfl_xor_sync(0xffffffffu, c, o); }
+  if ((threadIdx.x & 31) == 0) { wl[threadIdx.x >> 5] = l; wc[threadIdx.x >> 5] = c; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float L = 0.f; int C = 0;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) { L += wl[w]; C += wc[w]; }
+    const int cnt = *nonpad_count;
+    out3[0] = L / float(cnt) * inv_workers;  // 0/0 -> NaN for an all-PAD batch, as the reference
+    out3[1] = float(C);
+    out3[2] = float(cnt);
+  }
+}
+}  // namespace
+
+int vocab_ce_fwd_bwd(bf16* logits, int ldl, const long long* labels, int rows, int V, const int* nonpad_count, float inv_workers,
+                     float* row_loss, int* row_correct, int write_grad, cudaStream_t stream) {
+  if (ldl % 8) return set_error("vocab_ce: ld=%d must be a multiple of 8", ldl);
+  if (rows <= 0) return 0;
+  vocab_ce_kernel<<<rows, kCeThreads, 0, stream>>>(logits, ldl, labels, V, nonpad_count, inv_workers, row_loss, row_correct, write_grad);
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+int ce_finalize(const float* row_loss, const int* row_correct, const int* nonpad_count, int rows, float inv_workers, float* out3,
+                cudaStream_t stream) {
+  ce_finalize_kernel<<<1, 1024, 0, stream>>>(row_loss, row_correct, nonpad_count, rows, inv_workers, out3);
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+// ============================================================================ Adam + schedule
+namespace {
+// TF-form Adam (ResourceApplyAdam) with the reference's warm-up schedule evaluated on the device from
+// `iterations` (the value BEFORE this step's increment, so the very first step has lr == 0).
+__global__ void __launch_bounds__(256)
+adam_kernel(float4* __restrict__ w, float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v,
+            uint2* __restrict__ wb, size_t n4, const long long* __restrict__ iterations, AdamHyper h, int zero_grad) {
+  const float step = float(*iterations);
+  const float lr = h.rsqrt_d_model * fminf(step * h.warmup_pow_m15, 1.0f / sqrtf(step));
+  const float t = step + 1.0f;
+  const float alpha = lr * sqrtf(1.0f - powf(h.beta2, t)) / (1.0f - powf(h.beta1, t));
+  const float c1 = 1.0f - h.beta1, c2 = 1.0f - h.beta2;
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x) {
+    float4 W = w[i], M = m[i], V = v[i];
+    const float4 G = g[i];
+#define ADAM1(c)                                  \
+    M.c += (G.c - M.c) * c1;                      \
+    V.c += (G.c * G.c - V.c) * c2;                \
+    W.c -= (M.c * alpha) / (sqrtf(V.c) + h.eps);
+    ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
+#undef ADAM1
+    w[i] = W; m[i] = M; v[i] = V;
+    if (wb) { uint2 u; u.x = ptx::pack_bf16x2(W.x, W.y); u.y = ptx::pack_bf16x2(W.z, W.w); wb[i] = u; }
+    if (zero_grad) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+__global__ void increment_kernel(long long* c) { *c += 1; }
+}  // namespace
+
+int adam_step(float* w, float* g, float* m, float* v, bf16* w_bf16, size_t n, const long long* iterations_dev, AdamHyper h,
+              int zero_grad, cudaStream_t stream) {
+  if (n % 4) return set_error("adam: n=%zu must be a multiple of 4", n);
+  if (n == 0) return 0;
+  const size_t n4 = n / 4;
+  const int grid = int(std::min<size_t>((n4 + 255) / 256, size_t(num_sms()) * 8));
+  adam_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<float4*>(w), reinterpret_cast<float4*>(g), reinterpret_cast<float4*>(m),
+                                        reinterpret_cast<float4*>(v), reinterpret_cast<uint2*>(w_bf16), n4, iterations_dev, h, zero_grad);
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+int increment_counter(long long* iterations_dev, cudaStream_t stream) {
+  increment_kernel<<<1, 1, 0, stream>>>(iterations_dev);
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+// ============================================================================ helpers
+namespace {
+// out[c] (+)= sum_r x[r][c]; block = 16 column groups (4 bf16 each) x 16 row phases.
+__global__ void __launch_bounds__(256)
+colsum_kernel(const bf16* __restrict__ x, int ld, int rows, int cols, float* __restrict__ out, int accumulate) {
+  __shared__ float4 red[16][16];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const int col = blockIdx.x * 64 + tx * 4;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (col < cols) {
+    const bool fullv = col + 4 <= cols;
+#pragma unroll 4
+    for (int r = ty; r < rows; r += 16) {
+      const bf16* p = x + size_t(r) * ld + col;
+      if (fullv) {
+        const uint2 u = *reinterpret_cast<const uint2*>(p);
+        acc.x += ptx::bf16_lo(u.x); acc.y += ptx::bf16_hi(u.x); acc.z += ptx::bf16_lo(u.y); acc.w += ptx::bf16_hi(u.y);
+      } else {
+        acc.x += __bfloat162float(p[0]);
+        if (col + 1 < cols) acc.y += __bfloat162float(p[1]);
+        if (col + 2 < cols) acc.z += __bfloat162float(p[2]);
+      }
+    }
+  }
+  red[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0 && col < cols) {
+    float4 s = red[0][tx];
+    for (int i = 1; i < 16; ++i) { s.x += red[i][tx].x; s.y += red[i][tx].y; s.z += red[i][tx].z; s.w += red[i][tx].w; }
+    const float v[4] = {s.x, s.y, s.z, s.w};
+    for (int j = 0; j < 4; ++j)
+      if (col + j < cols) out[col + j] = accumulate ? out[col + j] + v[j] : v[j];
+  }
+}
+
+__global__ void cast_kernel(const float4* __restrict__ in, uint2* __restrict__ out, size_t n4) {
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x) {
+    const float4 f = in[i];
+    uint2 u; u.x = ptx::pack_bf16x2(f.x, f.y); u.y = ptx::pack_bf16x2(f.z, f.w);
+    out[i] = u;
+  }
+}
+
+__global__ void cast_back_kernel(const bf16* __restrict__ in, int ldi, float* __restrict__ out, int ldo, int rows, int cols) {
+  const size_t total = size_t(rows) * cols;
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < total; i += size_t(gridDim.x) * blockDim.x) {
+    const size_t r = i / cols, c = i % cols;
+    out[r * ldo + c] = __bfloat162float(in[r * ldi + c]);
+  }
+}
+}  // namespace
+
+int colsum_bf16(const bf16* x, int ld, int rows, int cols, float* out, int accumulate, cudaStream_t stream) {
+  if (ld % 4) return set_error("colsum: ld=%d must be a multiple of 4", ld);
+  if (cols <= 0) return 0;
+  colsum_kernel<<<(cols + 63) / 64, 256, 0, stream>>>(x, ld, rows, cols, out, accumulate);
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+int cast_f32_to_bf16(const float* in, bf16* out, size_t n, cudaStream_t stream) {
+  if (n % 4) return set_error("cast: n must be a multiple of 4");
+  if (n == 0) return 0;
+  const size_t n4 = n / 4;
+  const int grid = int(std::min<size_t>((n4 + 255) / 256, size_t(num_sms()) * 8));
+  cast_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<uint2*>(out), n4);
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+int cast_bf16_to_f32_2d(const bf16* in, int ldi, float* out, int ldo, int rows, int cols, cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0) return 0;
+  const size_t total = size_t(rows) * cols;
+  const int grid = int(std::min<size_t>((total + 255) / 256, size_t(num_sms()) * 8));
+  cast_back_kernel<<<grid, 256, 0, stream>>>(in, ldi, out, ldo, rows, cols);
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+}  // namespace b200xf

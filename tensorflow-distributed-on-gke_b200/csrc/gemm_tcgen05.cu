@@ -1,0 +1,397 @@
+// Persistent warp-specialised bf16 GEMM for sm_100a: TMA -> shared memory (128B swizzle) ->
+// tcgen05.mma (accumulators in TMEM, double buffered) -> tcgen05.ld epilogue.
+//
+// Replaces every tf.keras.layers.Dense matmul on the reference's hot path
+// (transformer_model.py:119-122,136-143,165 Q/K/V/O; :169-175 FFN; :333,347 vocab projection)
+// and their tape-derived backward products (__main__.py:112): forward  Y = X W + b,
+// dgrad dX = dY W^T, wgrad dW = X^T dY.  One kernel covers the three operand-layout cases through
+// the UMMA "major" bits, so no activation or weight is ever transposed in HBM:
+//   fwd   : A K-major  (X  [M,K]),  B MN-major (W  [K,N] as stored, [in,out])
+//   dgrad : A K-major  (dY [M,N]),  B K-major  (W  [K,N] read as [out=K][contract=N])
+//   wgrad : A MN-major (X  [tok,K] read as [contract=tok][out=K]), B MN-major (dY [tok,N])
+//
+// D[m][n] = sum_k A[m][k] * B[n][k];  fp32 accumulate; epilogue: +bias[n], ReLU, +residual or
+// ReLU-mask, output bf16 or fp32 (optionally atomically accumulated for split-K).
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "internal.h"
+#include "ptx.cuh"
+
+namespace b200xf {
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;       // 64 bf16 = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int kThreads = 192;  // warp0 TMA, warp1 MMA, warps 2-5 epilogue
+
+template <int BN>
+struct Cfg {
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kTmemCols = 2 * BN;  // double-buffered accumulator
+};
+
+struct GemmParams {
+  int M, N, K;
+  int tiles_m, tiles_n, splits, kb_per_split;
+  void* d; int ldd; int d_fp32; int accumulate;
+  const float* bias; int relu;
+  const __nv_bfloat16* resid; int ldr; int resid_op;  // 0 none, 1 add, 2 relu-mask
+  float alpha;
+};
+
+template <int BN, int A_MN, int B_MN>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* empty_bar = full_bar + C::kStages;
+  uint64_t* tmem_full = empty_bar + C::kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmap_a);
+    ptx::prefetch_tmap(&tmap_b);
+    for (int i = 0; i < C::kStages; ++i) { ptx::mbar_init(&full_bar[i], 1); ptx::mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tmem_full[i], 1); ptx::mbar_init(&tmem_empty[i], 4); }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, C::kTmemCols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
+  const int total_kb = (p.K + BK - 1) / BK;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer (one lane)
+    if (lane == 0) {
+      int s = 0; uint32_t ph = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int tm = t % p.tiles_m, tn = (t / p.tiles_m) % p.tiles_n, z = t / (p.tiles_m * p.tiles_n);
+        const int kb0 = z * p.kb_per_split;
+        const int kb1 = min(total_kb, kb0 + p.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          ptx::mbar_wait(&empty_bar[s], ph ^ 1);
+          uint8_t* sa = smem + s * C::kStageBytes;
+          uint8_t* sb = sa + C::kABytes;
+          ptx::mbar_expect_tx(&full_bar[s], C::kStageBytes);
+          if (A_MN) {
+#pragma unroll
+            for (int c = 0; c < BM / 64; ++c) ptx::tma_load_2d(sa + c * 8192, &tmap_a, &full_bar[s], tm * BM + c * 64, kb * BK);
+          } else {
+            ptx::tma_load_2d(sa, &tmap_a, &full_bar[s], kb * BK, tm * BM);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int c = 0; c < BN / 64; ++c) ptx::tma_load_2d(sb + c * 8192, &tmap_b, &full_bar[s], tn * BN + c * 64, kb * BK);
+          } else {
+            ptx::tma_load_2d(sb, &tmap_b, &full_bar[s], kb * BK, tn * BN);
+          }
+          if (++s == C::kStages) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (one lane)
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_bf16(BM, BN, A_MN, B_MN);
+      constexpr uint32_t a_lbo = A_MN ? 8192 : 16, b_lbo = B_MN ? 8192 : 16;
+      constexpr uint32_t a_kstep = A_MN ? (UMMA_K * 128) : (UMMA_K * 2);  // bytes per 16-wide k step
+      constexpr uint32_t b_kstep = B_MN ? (UMMA_K * 128) : (UMMA_K * 2);
+      int s = 0; uint32_t ph = 0; int it = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+        const int z = t / (p.tiles_m * p.tiles_n);
+        const int kb0 = z * p.kb_per_split;
+        const int kb1 = min(total_kb, kb0 + p.kb_per_split);
+        const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
+        ptx::mbar_wait(&tmem_empty[as], aph ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t tmem_d = tmem_base + as * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          ptx::mbar_wait(&full_bar[s], ph);
+          ptx::tc_fence_after();
+          const uint32_t sa = ptx::smem_u32(smem + s * C::kStageBytes);
+          const uint32_t sb = sa + C::kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t adesc = ptx::make_smem_desc(sa + k * a_kstep, a_lbo, 1024);
+            const uint64_t bdesc = ptx::make_smem_desc(sb + k * b_kstep, b_lbo, 1024);
+            ptx::umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          ptx::umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs retire
+          if (++s == C::kStages) { s = 0; ph ^= 1; }
+        }
+        ptx::umma_commit(&tmem_full[as]);  // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ epilogue (4 warps, 128 TMEM lanes)
+    const int quarter = warp & 3;  // TMEM lane quarter this warp may touch
+    int it = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      const int tm = t % p.tiles_m, tn = (t / p.tiles_m) % p.tiles_n, z = t / (p.tiles_m * p.tiles_n);
+      const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
+      ptx::mbar_wait(&tmem_full[as], aph);
+      ptx::tc_fence_after();
+      const int row = tm * BM + quarter * 32 + lane;
+      const bool row_ok = row < p.M;
+      const uint32_t taddr = tmem_base + as * BN + (uint32_t(quarter * 32) << 16);
+      const bool add_bias = p.bias != nullptr && z == 0;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = tn * BN + c * 32;
+        if (col0 >= p.N) break;  // warp-uniform
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(taddr + c * 32, v);
+        ptx::tmem_ld_wait();
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
+        const bool full = col0 + 32 <= p.N;
+        if (add_bias) {
+          if (full) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+              f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (col0 + j < p.N) f[j] += __ldg(p.bias + col0 + j);
+          }
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        if (p.resid_op && row_ok) {
+          const __nv_bfloat16* rp = p.resid + size_t(row) * p.ldr + col0;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float r[8];
+            if (col0 + g * 8 + 8 <= p.N) {
+              const uint4 u = *reinterpret_cast<const uint4*>(rp + g * 8);
+              r[0] = ptx::bf16_lo(u.x); r[1] = ptx::bf16_hi(u.x); r[2] = ptx::bf16_lo(u.y); r[3] = ptx::bf16_hi(u.y);
+              r[4] = ptx::bf16_lo(u.z); r[5] = ptx::bf16_hi(u.z); r[6] = ptx::bf16_lo(u.w); r[7] = ptx::bf16_hi(u.w);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) r[j] = (col0 + g * 8 + j < p.N) ? __bfloat162float(rp[g * 8 + j]) : 0.f;
+            }
+            if (p.resid_op == 1) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) f[g * 8 + j] += r[j];
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) f[g * 8 + j] = r[j] > 0.f ? f[g * 8 + j] : 0.f;
+            }
+          }
+        }
+        if (row_ok) {
+          if (p.d_fp32) {
+            float* dp = reinterpret_cast<float*>(p.d) + size_t(row) * p.ldd + col0;
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+              if (col0 + g * 4 + 4 <= p.N) {
+                if (p.accumulate) ptx::red_add_v4(dp + g * 4, f[g * 4], f[g * 4 + 1], f[g * 4 + 2], f[g * 4 + 3]);
+                else *reinterpret_cast<float4*>(dp + g * 4) = make_float4(f[g * 4], f[g * 4 + 1], f[g * 4 + 2], f[g * 4 + 3]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  if (col0 + g * 4 + j < p.N) {
+                    if (p.accumulate) atomicAdd(dp + g * 4 + j, f[g * 4 + j]); else dp[g * 4 + j] = f[g * 4 + j];
+                  }
+              }
+            }
+          } else {
+            __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(p.d) + size_t(row) * p.ldd + col0;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              if (col0 + g * 8 + 8 <= p.N) {
+                uint4 u;
+                u.x = ptx::pack_bf16x2(f[g * 8], f[g * 8 + 1]); u.y = ptx::pack_bf16x2(f[g * 8 + 2], f[g * 8 + 3]);
+                u.z = ptx::pack_bf16x2(f[g * 8 + 4], f[g * 8 + 5]); u.w = ptx::pack_bf16x2(f[g * 8 + 6], f[g * 8 + 7]);
+                *reinterpret_cast<uint4*>(dp + g * 8) = u;
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  if (col0 + g * 8 + j < p.N) dp[g * 8 + j] = __float2bfloat16(f[g * 8 + j]);
+              }
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tmem_empty[as]);
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(f);
+  });
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr; uint64_t inner, outer, ld; uint32_t box_outer;
+  bool operator<(const MapKey& o) const {
+    return std::tie(ptr, inner, outer, ld, box_outer) < std::tie(o.ptr, o.inner, o.outer, o.ld, o.box_outer);
+  }
+};
+std::map<MapKey, CUtensorMap> g_map_cache;
+std::mutex g_map_mutex;
+
+// 2-D bf16 tensor map: inner (contiguous) extent, outer extent, row pitch ld (elements); box = 64 x box_outer, 128B swizzle.
+int get_tmap(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_outer, CUtensorMap* out) {
+  MapKey key{ptr, inner, outer, ld, box_outer};
+  std::lock_guard<std::mutex> lock(g_map_mutex);
+  auto it = g_map_cache.find(key);
+  if (it != g_map_cache.end()) { *out = it->second; return 0; }
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return set_error("cuTensorMapEncodeTiled entry point unavailable");
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (ld % 8)) return set_error("gemm operand must be 16-byte aligned with ld % 8 == 0");
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {64, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error("cuTensorMapEncodeTiled failed (%d) inner=%llu outer=%llu ld=%llu", int(r),
+                                          (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld);
+  if (g_map_cache.size() > 8192) g_map_cache.clear();
+  g_map_cache[key] = *out;
+  return 0;
+}
+
+template <int BN, int A_MN, int B_MN>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t stream) {
+  auto kern = gemm_kernel<BN, A_MN, B_MN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmem);
+    if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gemm): %s", cudaGetErrorString(e));
+    attr_set = true;
+  }
+  kern<<<grid, kThreads, Cfg<BN>::kSmem, stream>>>(ta, tb, p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_error("gemm launch: %s", cudaGetErrorString(e));
+  count_launch();
+  return 0;
+}
+
+template <int BN>
+int launch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t s) {
+  if (!a_mn && b_mn) return launch<BN, 0, 1>(ta, tb, p, grid, s);
+  if (!a_mn && !b_mn) return launch<BN, 0, 0>(ta, tb, p, grid, s);
+  if (a_mn && b_mn) return launch<BN, 1, 1>(ta, tb, p, grid, s);
+  return launch<BN, 1, 0>(ta, tb, p, grid, s);
+}
+
+}  // namespace
+
+int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
+  if (a.M <= 0 || a.N <= 0 || a.K <= 0) return set_error("gemm: empty problem M=%d N=%d K=%d", a.M, a.N, a.K);
+  if (a.accumulate && !a.d_fp32) return set_error("gemm: accumulate requires fp32 output");
+  const int nsm = num_sms();
+  const int tiles_m = (a.M + BM - 1) / BM;
+  int bn = a.force_bn;
+  if (bn == 0) {
+    long best = -1;
+    for (int cand : {256, 128, 64}) {
+      if (cand > 64 && cand / 2 >= a.N) continue;  // do not waste more than half a tile
+      const long tiles = long(tiles_m) * ((a.N + cand - 1) / cand);
+      const long cost = ((tiles + nsm - 1) / nsm) * (cand + 64);
+      if (best < 0 || cost < best) { best = cost; bn = cand; }
+    }
+  }
+  if (bn != 64 && bn != 128 && bn != 256) return set_error("gemm: unsupported BN %d", bn);
+  const int tiles_n = (a.N + bn - 1) / bn;
+  const int total_kb = (a.K + BK - 1) / BK;
+  int splits = 1;
+  if (a.accumulate) {
+    splits = a.split_k;
+    if (splits <= 0) {
+      const int tiles = tiles_m * tiles_n;
+      splits = 1;
+      if (tiles * 2 <= nsm) splits = min(nsm / tiles, max(1, total_kb / 4));
+    }
+    splits = max(1, min(splits, total_kb));
+  }
+  int kb_per = (total_kb + splits - 1) / splits;
+  splits = (total_kb + kb_per - 1) / kb_per;
+
+  GemmParams p;
+  p.M = a.M; p.N = a.N; p.K = a.K;
+  p.tiles_m = tiles_m; p.tiles_n = tiles_n; p.splits = splits; p.kb_per_split = kb_per;
+  p.d = a.d; p.ldd = a.ldd; p.d_fp32 = a.d_fp32; p.accumulate = a.accumulate;
+  p.bias = a.bias; p.relu = a.relu;
+  p.resid = reinterpret_cast<const __nv_bfloat16*>(a.resid); p.ldr = a.ldr; p.resid_op = a.resid ? a.resid_op : 0;
+  p.alpha = a.alpha;
+
+  CUtensorMap ta, tb;
+  int rc;
+  if (a.a_mn) rc = get_tmap(a.a, a.M, a.K, a.lda, 64, &ta);
+  else rc = get_tmap(a.a, a.K, a.M, a.lda, BM, &ta);
+  if (rc) return rc;
+  if (a.b_mn) rc = get_tmap(a.b, a.N, a.K, a.ldb, 64, &tb);
+  else rc = get_tmap(a.b, a.K, a.N, a.ldb, bn, &tb);
+  if (rc) return rc;
+
+  const int total = tiles_m * tiles_n * splits;
+  const int grid = min(total, nsm);
+  switch (bn) {
+    case 64: return launch_major<64>(a.a_mn, a.b_mn, ta, tb, p, grid, stream);
+    case 128: return launch_major<128>(a.a_mn, a.b_mn, ta, tb, p, grid, stream);
+    default: return launch_major<256>(a.a_mn, a.b_mn, ta, tb, p, grid, stream);
+  }
+}
+
+void gemm_clear_tensor_map_cache() {
+  std::lock_guard<std::mutex> lock(g_map_mutex);
+  g_map_cache.clear();
+}
+
+}  // namespace b200xf

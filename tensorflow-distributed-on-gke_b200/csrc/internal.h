@@ -1,0 +1,108 @@
+// Internal (C++) interfaces shared by the kernels, the step orchestration and the C ABI.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <cstdint>
+
+namespace b200xf {
+
+typedef __nv_bfloat16 bf16;
+
+// ---- error / bookkeeping (thread-local last error; every launcher returns 0 on success)
+int set_error(const char* fmt, ...);
+const char* last_error_string();
+int num_sms();
+void count_launch(int n = 1);
+long long launches_total();
+
+#define B200XF_CUDA(expr)                                                                          \
+  do {                                                                                             \
+    cudaError_t _e = (expr);                                                                       \
+    if (_e != cudaSuccess) return ::b200xf::set_error("%s: %s", #expr, cudaGetErrorString(_e));    \
+  } while (0)
+#define B200XF_TRY(expr)          \
+  do {                            \
+    int _rc = (expr);             \
+    if (_rc) return _rc;          \
+  } while (0)
+
+// ---- GEMM  D[M,N] = alpha * A[M,K] . B[N,K]^T (+bias)(relu)(+resid | *relumask(resid))
+struct GemmArgs {
+  const void* a = nullptr; int lda = 0; int a_mn = 0;  // a_mn=0: stored [M][K]; 1: stored [K][M]
+  const void* b = nullptr; int ldb = 0; int b_mn = 0;  // b_mn=0: stored [N][K]; 1: stored [K][N]
+  void* d = nullptr; int ldd = 0; int d_fp32 = 0;
+  int accumulate = 0;  // fp32 atomic accumulate into d (enables split-K)
+  int split_k = 0;     // 0 = auto
+  int M = 0, N = 0, K = 0;
+  const float* bias = nullptr;
+  int relu = 0;
+  const void* resid = nullptr; int ldr = 0; int resid_op = 0;  // 1 add, 2 relu-mask
+  float alpha = 1.f;
+  int force_bn = 0;
+};
+int gemm_bf16(const GemmArgs& a, cudaStream_t stream);
+void gemm_clear_tensor_map_cache();
+
+// ---- attention (fused, masks derived in-tile from token ids; transformer_model.py:73-109,350-363)
+struct AttnArgs {
+  const bf16* q = nullptr; int ldq = 0;   // [B*Sq, ldq], head h at column h*dk
+  const bf16* k = nullptr; int ldk = 0;   // [B*Sk, ldk]
+  const bf16* v = nullptr; int ldv = 0;
+  bf16* o = nullptr; int ldo = 0;         // [B*Sq, ldo]
+  float* lse = nullptr;                   // [B,H,Sq] log2-domain logsumexp of scaled+masked scores
+  const long long* key_tokens = nullptr;  // [B,Sk] int64; key j masked iff token == 0
+  int causal = 0;                         // additionally mask j > i
+  int B = 0, H = 0, Sq = 0, Sk = 0, dk = 0;
+  // backward only
+  const bf16* d_o = nullptr; int lddo = 0;
+  bf16* dq = nullptr; int lddq = 0;
+  bf16* dk_out = nullptr; int lddk = 0;
+  bf16* dv_out = nullptr; int lddv = 0;
+  float* delta = nullptr;                 // scratch [B,H,Sq]
+  float* probs = nullptr;                 // optional fwd output [B,H,Sq,Sk] fp32 (inference API only)
+};
+int attention_fwd(const AttnArgs& a, cudaStream_t stream);
+int attention_bwd(const AttnArgs& a, cudaStream_t stream);
+
+// ---- LayerNorm (+ optional residual add) fwd / bwd (transformer_model.py:187-188,198,204)
+int layernorm_fwd(const bf16* x, const bf16* resid, const float* gamma, const float* beta, bf16* y, bf16* z_out,
+                  float* mean, float* rstd, int rows, int d, float eps, cudaStream_t stream);
+// dz = LN'(dy); dgamma/dbeta (+= over rows, overwritten), dcol = colsum(dz) (bias grad of the producing GEMM, may be null).
+// scratch: floats [ln_bwd_scratch_floats(rows,d)] + one unsigned counter that must be zero on entry (left zero on exit).
+size_t ln_bwd_scratch_floats(int rows, int d);
+int layernorm_bwd(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const float* gamma, bf16* dz,
+                  float* dgamma, float* dbeta, float* dcol, int rows, int d, float* scratch, unsigned* counter,
+                  cudaStream_t stream);
+
+// ---- embedding * sqrt(d) + positional encoding (transformer_model.py:273-275,305-307)
+int embed_pe_fwd(const long long* tokens, const float* table, int vocab, const float* pe, bf16* out, int B, int S, int d,
+                 cudaStream_t stream);
+size_t embed_bwd_scratch_bytes(int n_tokens);
+int embed_bwd(const long long* tokens, const bf16* dx, float* dtable, int vocab, int n_tokens, int d, void* scratch,
+              size_t scratch_bytes, cudaStream_t stream);
+
+// ---- targets: shift, count (__main__.py:106-107; transformer_model.py:12)
+int prep_targets(const long long* target, long long* tgt_in, long long* labels, int* nonpad_count, int B, int T_plus_1,
+                 cudaStream_t stream);
+
+// ---- masked softmax cross-entropy over the vocab, fwd + bwd in place (transformer_model.py:7-26)
+// logits bf16 [rows, ldl]; writes dlogits in place; row_loss/row_correct fp32/int per row; finalize reduces them.
+int vocab_ce_fwd_bwd(bf16* logits, int ldl, const long long* labels, int rows, int V, const int* nonpad_count,
+                     float inv_workers, float* row_loss, int* row_correct, int write_grad, cudaStream_t stream);
+int ce_finalize(const float* row_loss, const int* row_correct, const int* nonpad_count, int rows, float inv_workers,
+                float* out3 /* loss, acc_num, acc_den */, cudaStream_t stream);
+
+// ---- Adam + LR schedule over a flat fp32 range (__main__.py:56-73,113-114)
+struct AdamHyper { float beta1, beta2, eps, rsqrt_d_model, warmup_pow_m15; };  // warmup_pow_m15 = float(warmup ** -1.5)
+int adam_step(float* w, float* g, float* m, float* v, bf16* w_bf16, size_t n, const long long* iterations_dev,
+              AdamHyper h, int zero_grad, cudaStream_t stream);
+int increment_counter(long long* iterations_dev, cudaStream_t stream);
+
+// ---- small helpers
+int colsum_bf16(const bf16* x, int ld, int rows, int cols, float* out, int accumulate, cudaStream_t stream);
+int cast_f32_to_bf16(const float* in, bf16* out, size_t n, cudaStream_t stream);
+int cast_bf16_to_f32_2d(const bf16* in, int ldi, float* out, int ldo, int rows, int cols, cudaStream_t stream);
+
+}  // namespace b200xf

@@ -1,0 +1,239 @@
+"""Per-kernel parity on the GPU, through the C ABI (ctypes): each CUDA kernel against a plain torch fp32
+restatement of the same op on the same (bf16-rounded) inputs.  Tolerances are stated per test."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import b200xf
+from b200xf import kernels as K
+
+DEV = "cuda"
+
+
+def _bf(x):
+    return x.to(torch.bfloat16)
+
+
+def _rel(a, b):
+    a = a.float(); b = b.float()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+# ------------------------------------------------------------------------------------------ GEMM
+LAYOUTS = {"fwd": (False, True), "dgrad": (False, False), "wgrad": (True, True), "mn_k": (True, False)}
+SHAPES = [(128, 128, 64), (256, 256, 128), (300, 200, 136), (2560, 384, 128), (130, 7010, 128), (512, 520, 4096)]
+
+
+def _make_operand(rows_logical, k, mn_major, g):
+    """Returns (stored tensor view with 8-aligned pitch, logical [rows, k] fp32 of the bf16 values)."""
+    if mn_major:  # stored [k, rows]
+        ld = (rows_logical + 7) // 8 * 8
+        buf = _bf(torch.randn(k, ld, device=DEV, generator=g))
+        view = buf[:, :rows_logical]
+        return view, view.float().t().contiguous()
+    ld = (k + 7) // 8 * 8
+    buf = _bf(torch.randn(rows_logical, ld, device=DEV, generator=g))
+    view = buf[:, :k]
+    return view, view.float()
+
+
+@pytest.mark.parametrize("layout", list(LAYOUTS))
+@pytest.mark.parametrize("shape", SHAPES)
+@pytest.mark.parametrize("bn", [0, 64, 128, 256])
+def test_gemm_layouts(layout, shape, bn):
+    M, N, Kd = shape
+    a_mn, b_mn = LAYOUTS[layout]
+    g = torch.Generator(device=DEV).manual_seed(hash((layout, shape)) % 2**31)
+    a, a_log = _make_operand(M, Kd, a_mn, g)
+    b, b_log = _make_operand(N, Kd, b_mn, g)
+    ref = a_log @ b_log.t()
+    ldn = (N + 7) // 8 * 8
+    out = torch.full((M, ldn), float("nan"), device=DEV, dtype=torch.float32)[:, :N]
+    K.gemm(a, b, a_mn=a_mn, b_mn=b_mn, out=out, force_bn=bn)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out).all(), f"non-finite output {layout} {shape} bn={bn}"
+    err = _rel(out, ref)
+    assert err < 2e-5, f"{layout} {shape} bn={bn}: rel err {err}"  # fp32 accumulate of exact bf16 products
+
+
+def test_gemm_epilogues():
+    g = torch.Generator(device=DEV).manual_seed(7)
+    M, N, Kd = 384, 320, 192
+    x = _bf(torch.randn(M, Kd, device=DEV, generator=g)); w = _bf(torch.randn(Kd, N, device=DEV, generator=g) * 0.1)
+    bias = torch.randn(N, device=DEV, generator=g); resid = _bf(torch.randn(M, N, device=DEV, generator=g))
+    base = x.float() @ w.float()
+    y = K.gemm(x, w, b_mn=True, bias=bias)
+    assert _rel(y, base + bias) < 4e-3  # bf16 output rounding (2^-9 relative per element)
+    y = K.gemm(x, w, b_mn=True, bias=bias, relu=True)
+    assert _rel(y, torch.relu(base + bias)) < 4e-3
+    y = K.gemm(x, w, b_mn=True, bias=bias, resid=resid, resid_op=1)
+    assert _rel(y, base + bias + resid.float()) < 4e-3
+    y = K.gemm(x, w, b_mn=True, resid=resid, resid_op=2)
+    assert _rel(y, base * (resid.float() > 0)) < 4e-3
+    y = K.gemm(x, w, b_mn=True, alpha=0.5, out_fp32=True)
+    assert _rel(y, 0.5 * base) < 2e-5
+
+
+@pytest.mark.parametrize("split_k", [0, 1, 3, 8])
+def test_gemm_wgrad_accumulate_split_k(split_k):
+    g = torch.Generator(device=DEV).manual_seed(11)
+    tokens, Kd, N = 4096, 256, 200
+    x = _bf(torch.randn(tokens, Kd, device=DEV, generator=g)); dy = _bf(torch.randn(tokens, 208, device=DEV, generator=g))[:, :N]
+    acc = torch.ones((Kd, 208), device=DEV, dtype=torch.float32)[:, :N]
+    K.gemm(x, dy, a_mn=True, b_mn=True, out=acc, accumulate=True, split_k=split_k)
+    ref = 1.0 + x.float().t() @ dy.float()
+    assert _rel(acc, ref) < 2e-5
+
+
+# ------------------------------------------------------------------------------------------ attention
+def _attn_ref(q, k, v, key_tokens, causal, H):
+    """transformer_model.py:73-109 + masks :56-70,:350-363, in fp32."""
+    B, Sq, D = q.shape; Sk = k.shape[1]; dk = D // H
+    sp = lambda x: x.float().reshape(B, -1, H, dk).permute(0, 2, 1, 3)
+    logits = sp(q) @ sp(k).transpose(-1, -2) / math.sqrt(dk)
+    mask = (key_tokens == 0).float()[:, None, None, :]
+    if causal:
+        la = 1.0 - torch.tril(torch.ones(Sq, Sk, device=q.device))
+        mask = torch.maximum(mask, la)
+    logits = logits + mask * -1e9
+    w = torch.softmax(logits, -1)
+    return (w @ sp(v)).permute(0, 2, 1, 3).reshape(B, Sq, D), w
+
+
+ATTN_CASES = [  # B, H, Sq, Sk, dk, causal, pad_first_token
+    (2, 8, 40, 40, 16, False, False), (2, 8, 40, 40, 16, True, False), (3, 4, 40, 33, 32, False, False),
+    (2, 8, 128, 128, 64, True, False), (2, 8, 128, 128, 64, False, False), (1, 2, 200, 77, 64, False, False),
+    (2, 2, 70, 70, 16, True, True), (1, 2, 300, 300, 64, True, False),
+]
+
+
+@pytest.mark.parametrize("case", ATTN_CASES)
+def test_attention_fwd_bwd(case):
+    B, H, Sq, Sk, dk, causal, pad_first = case
+    g = torch.Generator(device=DEV).manual_seed(3)
+    D = H * dk
+    qkv = _bf(torch.randn(B, max(Sq, Sk), 3 * D, device=DEV, generator=g))
+    q = qkv[:, :Sq, :D]; k = qkv[:, :Sk, D:2 * D]; v = qkv[:, :Sk, 2 * D:]
+    toks = torch.randint(4, 100, (B, Sk), device=DEV, generator=g)
+    for b in range(B):
+        toks[b, Sk - (b * 5 + 3) % (Sk // 2):] = 0  # ragged right padding
+    if pad_first:
+        toks[0, :3] = 0  # fully masked causal rows -> must come out uniform like the reference
+    o, lse = K.attention_fwd(q, k, v, toks, causal, H)
+    qr, kr, vr = (t.float().detach().requires_grad_(True) for t in (q, k, v))
+    ref, _ = _attn_ref(qr, kr, vr, toks, causal, H)
+    assert torch.isfinite(o.float()).all()
+    err = float((o.float() - ref).abs().max())
+    assert err < 2e-2, f"{case}: fwd max abs err {err}"  # bf16 probabilities and output
+    d_o = _bf(torch.randn(B, Sq, D, device=DEV, generator=g))
+    dq, dk_, dv = K.attention_bwd(q, k, v, o, lse, d_o, toks, causal, H)
+    ref.backward(d_o.float())
+    for name, got, want in (("dq", dq, qr.grad), ("dk", dk_, kr.grad), ("dv", dv, vr.grad)):
+        assert torch.isfinite(got.float()).all(), f"{case}: {name} not finite"
+        e = _rel(got, want)
+        assert e < 2e-2, f"{case}: {name} rel err {e}"
+
+
+# ------------------------------------------------------------------------------------------ LayerNorm
+@pytest.mark.parametrize("rows,d", [(2560, 128), (4096, 512), (1000, 1024), (37, 264)])
+def test_layernorm_fwd_bwd(rows, d):
+    g = torch.Generator(device=DEV).manual_seed(5)
+    x = _bf(torch.randn(rows, d, device=DEV, generator=g)); r = _bf(torch.randn(rows, d, device=DEV, generator=g))
+    gamma = torch.randn(d, device=DEV, generator=g); beta = torch.randn(d, device=DEV, generator=g)
+    y, z, mean, rstd = K.layernorm_residual_fwd(x, r, gamma, beta, 1e-6, want_z=True)
+    zr = _bf(x.float() + r.float()).float().requires_grad_(True)
+    assert torch.equal(z.float(), zr.detach())
+    gr = gamma.clone().requires_grad_(True); br = beta.clone().requires_grad_(True)
+    ref = torch.nn.functional.layer_norm(zr, (d,), gr, br, 1e-6)
+    assert float((y.float() - ref).abs().max()) < 4e-2 and _rel(y, ref) < 4e-3  # bf16 output
+    np.testing.assert_allclose(mean.cpu(), zr.detach().mean(-1).cpu(), atol=1e-5)
+    dy = _bf(torch.randn(rows, d, device=DEV, generator=g))
+    y2, _, mean2, rstd2 = K.layernorm_residual_fwd(z, None, gamma, beta, 1e-6)
+    assert torch.equal(y2, y)
+    dz, dgamma, dbeta, dcol = K.layernorm_residual_bwd(dy, z, mean, rstd, gamma)
+    ref.backward(dy.float())
+    assert _rel(dz, zr.grad) < 4e-3
+    assert _rel(dgamma, gr.grad) < 1e-4 and _rel(dbeta, br.grad) < 1e-4  # fp32 sums
+    assert _rel(dcol, dz.float().sum(0)) < 1e-5
+    # run twice with the same scratch: the counter must have been left at zero; result bit-identical (deterministic)
+    scratch = K.layernorm_bwd_scratch(rows, d, DEV)
+    a = K.layernorm_residual_bwd(dy, z, mean, rstd, gamma, scratch)
+    b = K.layernorm_residual_bwd(dy, z, mean, rstd, gamma, scratch)
+    for u, w in zip(a, b):
+        assert torch.equal(u, w)
+
+
+# ------------------------------------------------------------------------------------------ embedding
+def test_embedding_fwd_bit_exact_and_bwd():
+    g = torch.Generator(device=DEV).manual_seed(9)
+    V, d, B, S = 7765, 128, 64, 40
+    table = (torch.rand(V, d, device=DEV, generator=g) - 0.5) * 0.1
+    pe = K.positional_encoding(1000, d).to(DEV)
+    toks = torch.randint(0, V, (B, S), device=DEV, generator=g)
+    toks[:, -5:] = 0
+    out = K.embed_pe_fwd(toks, table, pe)
+    ref = table[toks] * np.float32(math.sqrt(d)) + pe[:S]
+    assert torch.equal(out, _bf(ref))  # gather bit-exact; one fp32 mul+add then a bf16 round
+    dx = _bf(torch.randn(B, S, d, device=DEV, generator=g))
+    dt = K.embed_pe_bwd(toks, dx, V)
+    want = torch.zeros(V, d, device=DEV).index_add_(0, toks.reshape(-1), dx.float().reshape(-1, d)) * np.float32(math.sqrt(d))
+    assert _rel(dt, want) < 1e-6
+    assert torch.equal(dt, K.embed_pe_bwd(toks, dx, V))  # deterministic
+    assert torch.count_nonzero(dt[torch.bincount(toks.reshape(-1), minlength=V) == 0]) == 0
+
+
+def test_positional_encoding_matches_reference_kat():
+    pe = K.positional_encoding(1000, 128)
+    assert pe[0].tolist() == [0.0, 1.0] * 64
+    np.testing.assert_allclose(pe[1, :4].numpy(), [0.841471, 0.5403023, 0.7617204, 0.6479058], rtol=2e-6)
+    np.testing.assert_allclose(pe[1, -2:].numpy(), [1.1547821e-4, 1.0], rtol=2e-6)
+
+
+# ------------------------------------------------------------------------------------------ cross-entropy
+@pytest.mark.parametrize("rows,V,workers", [(2560, 7010, 1), (512, 32000, 3), (64, 50, 1)])
+def test_vocab_ce(rows, V, workers):
+    g = torch.Generator(device=DEV).manual_seed(13)
+    ld = (V + 7) // 8 * 8
+    buf = _bf(torch.randn(rows, ld, device=DEV, generator=g) * 3)
+    logits = buf[:, :V]
+    labels = torch.randint(1, V, (rows,), device=DEV, generator=g)
+    labels[::7] = 0
+    lr = logits.float().detach().clone().requires_grad_(True)
+    mask = (labels != 0).float()
+    lse = torch.logsumexp(lr, -1)
+    loss = ((lse - lr.gather(-1, labels[:, None])[:, 0]) * mask).sum() / mask.sum() / workers
+    loss.backward()
+    correct = ((lr.argmax(-1) == labels) & (labels != 0)).sum()
+    out3 = K.vocab_ce_fwd_bwd(buf, labels, V, workers, write_grad=True)
+    assert abs(float(out3[0]) - float(loss)) < 2e-5 * max(1.0, abs(float(loss)))
+    assert int(out3[1]) == int(correct) and int(out3[2]) == int(mask.sum())
+    assert _rel(buf[:, :V], lr.grad) < 5e-3  # bf16 gradient
+    assert torch.count_nonzero(buf[labels == 0][:, :V]) == 0
+
+
+# ------------------------------------------------------------------------------------------ Adam
+@pytest.mark.parametrize("iterations", [0, 1, 4000, 12345])
+def test_adam_tf_form(iterations):
+    from oracle import transformer_oracle as O
+    g = torch.Generator(device=DEV).manual_seed(17)
+    n = 1 << 16
+    w = torch.randn(n, device=DEV, generator=g); gr = torch.randn(n, device=DEV, generator=g) * 1e-3
+    gr[:100] = 1e-6
+    m = torch.randn(n, device=DEV, generator=g) * 1e-3; v = torch.rand(n, device=DEV, generator=g) * 1e-6
+    it = torch.tensor([iterations], device=DEV, dtype=torch.int64)
+    lr = O.learning_rate(iterations, 128)
+    we, me, ve = O.adam_update_numpy(w.cpu().numpy(), gr.cpu().numpy(), m.cpu().numpy(), v.cpu().numpy(), iterations, lr)
+    w0 = w.clone()
+    shadow = torch.empty(n, device=DEV, dtype=torch.bfloat16)
+    K.adam_step(w, gr, m, v, it, 128, w_bf16=shadow)
+    if iterations == 0:
+        assert torch.equal(w, w0)  # lr(0) == 0: weights bit-identical
+    np.testing.assert_allclose(m.cpu().numpy(), me, rtol=3e-7, atol=0)
+    np.testing.assert_allclose(v.cpu().numpy(), ve, rtol=3e-7, atol=0)
+    upd, upd_e = (w - w0).cpu().numpy(), we - w0.cpu().numpy()
+    np.testing.assert_allclose(w.cpu().numpy(), we, rtol=0, atol=2e-6 * float(np.abs(upd_e).max() + 1e-30) + 2.4e-7 * float(w0.abs().max()))
+    assert torch.equal(shadow, w.to(torch.bfloat16))
