@@ -77,21 +77,22 @@ int b200xf_forward(b200xf_ctx* ctx, const int64_t* inp, const int64_t* tgt_in, i
 
 /* ---- train_step (__main__.py:105-117): shift, forward, local_loss_function(.., workers_count), backward,
  * gradient all-reduce when a communicator is attached (cluster/cluster.py:66), Adam + schedule in place,
- * accuracy counts.  inp [B,S], target [B,T+1] int64.  out3 = {loss (already / workers_count),
- * accuracy numerator, accuracy denominator} fp32.
- *   _device : DEVICE token pointers, DEVICE out3, fully asynchronous.
- *   _host   : HOST token pointers (pinned for async copies), HOST out3; copies in, runs, copies the three
+ * accuracy counts.  inp [B,S], target [B,T+1] int64.  out6 (fp32) = {local loss (already / workers_count),
+ * accuracy numerator, accuracy denominator, then the same three SUMmed over replicas — what
+ * strategy.reduce(SUM, ...) returns at __main__.py:131-132; equal to the first three without a communicator}.
+ *   _device : DEVICE token pointers, DEVICE out6, fully asynchronous.
+ *   _host   : HOST token pointers (pinned for async copies), HOST out6; copies in, runs, copies the six
  *             scalars back and synchronises the stream — the reference-facing call. */
 int b200xf_train_step_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T_plus_1,
-                             int workers_count, float* out3);
+                             int workers_count, float* out6);
 int b200xf_train_step_host(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T_plus_1,
-                           int workers_count, float* out3);
+                           int workers_count, float* out6);
 /* test_step (__main__.py:119-125): forward + loss(workers_count=1) + accuracy, no update.  DEVICE pointers. */
 int b200xf_eval_step_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T_plus_1,
-                            float* out3);
+                            float* out6);
 /* Run only forward+loss+backward (no all-reduce, no Adam): gradients are left in grad_ptr. */
 int b200xf_forward_backward_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T_plus_1,
-                                   int workers_count, float* out3);
+                                   int workers_count, float* out6);
 int b200xf_synchronize(b200xf_ctx* ctx);
 
 /* ---- MultiWorkerMirroredStrategy's implicit SUM all-reduce (cluster/cluster.py:66; __main__.py:113-114,
@@ -116,7 +117,7 @@ int b200xf_gemm_bf16(const void* a, int lda, int a_mn, const void* b, int ldb, i
 
 /* scaled_dot_product_attention + masks + split/merge heads (transformer_model.py:56-70,73-109,124-131,160-163).
  * q [B*Sq, ldq], k/v [B*Sk, ld*], o [B*Sq, ldo] bf16, head h in columns [h*dk,(h+1)*dk); key_tokens [B,Sk] int64;
- * lse fp32 [B,H,Sq] (log2 domain). */
+ * lse fp32 [B,H,Sq,2] = {row max, log2(row sum)} of the scaled, masked scores in the log2 domain. */
 int b200xf_attention_fwd(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, void* o, int ldo,
                          float* lse, const int64_t* key_tokens, int causal, int B, int H, int Sq, int Sk, int dk,
                          void* stream);
@@ -129,8 +130,9 @@ int b200xf_attention_bwd(const void* q, int ldq, const void* k, int ldk, const v
  * z_out (optional) receives x+resid; mean/rstd fp32 [rows]. */
 int b200xf_layernorm_residual_fwd(const void* x, const void* resid, const float* gamma, const float* beta, void* y,
                                   void* z_out, float* mean, float* rstd, int rows, int d, float eps, void* stream);
-/* Backward.  dcol (optional) = column sums of dz.  scratch: b200xf_layernorm_bwd_scratch_bytes(rows, d) bytes of
- * device memory whose last 4 bytes (a counter) must be zero on entry; they are zero again on return. */
+/* Backward.  dcol (optional) = column sums of dz (the bias gradient of the Dense that produced x).  scratch:
+ * b200xf_layernorm_bwd_scratch_bytes(rows, d) bytes of device memory; it receives per-block partial column sums that a
+ * second launch adds up in a fixed order (deterministic); its previous contents do not matter. */
 size_t b200xf_layernorm_bwd_scratch_bytes(int rows, int d);
 int b200xf_layernorm_residual_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const float* gamma,
                                   void* dz, float* dgamma, float* dbeta, float* dcol, int rows, int d, void* scratch,

@@ -11,5 +11,5 @@ for g in "${groups[@]}"; do
     *) sel="tests/test_kernels_gpu.py -k $g" ;;
   esac
   echo "=== $g"
-  timeout 600 python -m pytest $sel -q -m gpu --timeout 120 --timeout-method=thread -x -q 2>&1 | tail -25 | tee gpurun_out/test_$g.log
+  timeout 600 python -m pytest $sel -q -m gpu --timeout 120 --timeout-method=thread $XFLAG -q 2>&1 | grep -v "Warning\|warnings.html\|^$\|Triggered\|Consider" | tail -${TAILN:-40} | tee gpurun_out/test_$g.log
 done

@@ -127,14 +127,12 @@ int b200xf_layernorm_residual_fwd(const void* x, const void* resid, const float*
   return layernorm_fwd(static_cast<const bf16*>(x), static_cast<const bf16*>(resid), gamma, beta, static_cast<bf16*>(y),
                        static_cast<bf16*>(z_out), mean, rstd, rows, d, eps, static_cast<cudaStream_t>(stream));
 }
-size_t b200xf_layernorm_bwd_scratch_bytes(int rows, int d) { return ln_bwd_scratch_floats(rows, d) * sizeof(float) + 4; }
+size_t b200xf_layernorm_bwd_scratch_bytes(int rows, int d) { return ln_bwd_scratch_floats(rows, d) * sizeof(float); }
 int b200xf_layernorm_residual_bwd(const void* dy, const void* z, const float* mean, const float* rstd, const float* gamma, void* dz,
                                   float* dgamma, float* dbeta, float* dcol, int rows, int d, void* scratch, void* stream) {
   if (!scratch) return set_error("layernorm_bwd: scratch is null");
-  float* fs = static_cast<float*>(scratch);
-  unsigned* counter = reinterpret_cast<unsigned*>(fs + ln_bwd_scratch_floats(rows, d));
   return layernorm_bwd(static_cast<const bf16*>(dy), static_cast<const bf16*>(z), mean, rstd, gamma, static_cast<bf16*>(dz), dgamma,
-                       dbeta, dcol, rows, d, fs, counter, static_cast<cudaStream_t>(stream));
+                       dbeta, dcol, rows, d, static_cast<float*>(scratch), static_cast<cudaStream_t>(stream));
 }
 
 int b200xf_embed_pe_fwd(const int64_t* tokens, const float* table, int vocab, const float* pe, void* out, int B, int S, int d, void* stream) {

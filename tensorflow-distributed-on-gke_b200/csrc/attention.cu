@@ -209,7 +209,10 @@ attn_fwd_kernel(const KernelArgs p) {
 #pragma unroll
       for (int nb = 0; nb < DK / 8; ++nb)
         *reinterpret_cast<uint32_t*>(dst + nb * 8 + t4 * 2) = ptx::pack_bf16x2(o[nb][r * 2] * inv[r], o[nb][r * 2 + 1] * inv[r]);
-      if (t4 == 0 && p.lse) p.lse[(size_t(b) * p.H + h) * p.Sq + row] = m[r] + log2f(l[r]);
+      if (t4 == 0 && p.lse) {  // kept as two terms: for a fully masked row m = -1.44e9 and would absorb log2(l)
+        float2* dst2 = reinterpret_cast<float2*>(p.lse) + (size_t(b) * p.H + h) * p.Sq + row;
+        *dst2 = make_float2(m[r], log2f(l[r]));
+      }
     }
   }
 }
@@ -229,7 +232,7 @@ attn_bwd_dq_kernel(const KernelArgs p) {
   const int r0 = q0 + warp * 16 + g;
 
   // delta = rowsum(dO * O) for this thread's two rows (each row's DK columns are spread over the quad)
-  float delta[2] = {0.f, 0.f}, lse[2] = {0.f, 0.f};
+  float delta[2] = {0.f, 0.f}, lse_m[2] = {0.f, 0.f}, lse_l[2] = {0.f, 0.f};
 #pragma unroll
   for (int r = 0; r < 2; ++r) {
     const int row = r0 + r * 8;
@@ -242,7 +245,8 @@ attn_bwd_dq_kernel(const KernelArgs p) {
         acc += ptx::bf16_lo(uo) * ptx::bf16_lo(ud) + ptx::bf16_hi(uo) * ptx::bf16_hi(ud);
       }
       delta[r] = acc;
-      lse[r] = p.lse[(size_t(b) * p.H + h) * p.Sq + row];
+      const float2 ml = reinterpret_cast<const float2*>(p.lse)[(size_t(b) * p.H + h) * p.Sq + row];
+      lse_m[r] = ml.x; lse_l[r] = ml.y;
     }
     delta[r] = quad_sum(delta[r]);
     if (t4 == 0 && row < p.Sq) p.delta[(size_t(b) * p.H + h) * p.Sq + row] = delta[r];
@@ -287,7 +291,7 @@ attn_bwd_dq_kernel(const KernelArgs p) {
         const int mk = sMask[jl];
         float v = s[nb][e] * p.scale_log2;
         if (mk == 1 || (p.causal && k0 + jl > row)) v = kMasked;
-        const float pr = (mk == 2) ? 0.f : exp2f(v - lse[e >> 1]);
+        const float pr = (mk == 2) ? 0.f : exp2f((v - lse_m[e >> 1]) - lse_l[e >> 1]);
         s[nb][e] = pr * (dp[nb][e] - delta[e >> 1]);  // dS
       }
     }
@@ -312,7 +316,7 @@ template <int DK>
 __global__ void __launch_bounds__(kWarps * 32)
 attn_bwd_dkv_kernel(const KernelArgs p) {
   __shared__ __align__(16) typename Smem<DK>::Tile sK, sQ, sDO;  // sK is reused for V while building fragments
-  __shared__ float sLse[kTile], sDelta[kTile];
+  __shared__ float sLseM[kTile], sLseL[kTile], sDelta[kTile];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
   const int b = blockIdx.z, h = blockIdx.y, k0 = blockIdx.x * kTile;
   const bf16* Q = p.q + size_t(b) * p.Sq * p.ldq;
@@ -345,7 +349,8 @@ attn_bwd_dkv_kernel(const KernelArgs p) {
     load_tile<DK>(sDO, DO, p.lddo, q0, p.Sq, h * DK);
     if (threadIdx.x < kTile) {
       const int i = q0 + threadIdx.x;
-      sLse[threadIdx.x] = (i < p.Sq) ? p.lse[(size_t(b) * p.H + h) * p.Sq + i] : INFINITY;  // exp2(x - inf) = 0
+      const float2 ml = (i < p.Sq) ? reinterpret_cast<const float2*>(p.lse)[(size_t(b) * p.H + h) * p.Sq + i] : make_float2(INFINITY, 0.f);
+      sLseM[threadIdx.x] = ml.x; sLseL[threadIdx.x] = ml.y;  // exp2(x - inf) = 0 for rows past Sq
       sDelta[threadIdx.x] = (i < p.Sq) ? p.delta[(size_t(b) * p.H + h) * p.Sq + i] : 0.f;
     }
     __syncthreads();
@@ -364,7 +369,7 @@ attn_bwd_dkv_kernel(const KernelArgs p) {
         const int mk = kmask[e >> 1];
         float v = st[nb][e] * p.scale_log2;
         if (mk == 1 || (p.causal && key > q0 + il)) v = kMasked;
-        const float pr = (mk == 2) ? 0.f : exp2f(v - sLse[il]);
+        const float pr = (mk == 2) ? 0.f : exp2f((v - sLseM[il]) - sLseL[il]);
         pt[nb][e] = pr;
         st[nb][e] = pr * (dpt[nb][e] - sDelta[il]);   // dS^T
       }

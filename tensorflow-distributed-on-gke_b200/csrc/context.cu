@@ -239,16 +239,24 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   // ---- workspace arena
   const size_t N = size_t(hp.max_tokens);
   const size_t nd = N * d, nff = N * dff;
-  const size_t ln_scr = ln_bwd_scratch_floats(int(N), d);
+  // column-sum partials of one backward pass: 5L LayerNorms, per-layer QKV / FFN1 / (Q2) bias sums, K|V and vocab bias sums
+  {
+    const int n = int(N);
+    size_t f = size_t(5 * L) * (ln_bwd_scratch_floats(n, d) + 64);
+    f += size_t(2 * L) * (size_t(colsum_parts(n, 3 * d)) * 3 * d + 64) + size_t(2 * L) * (size_t(colsum_parts(n, dff)) * dff + 64);
+    f += size_t(L) * (size_t(colsum_parts(n, d)) * d + 64) + size_t(colsum_parts(n, L * 2 * d)) * L * 2 * d + 64;
+    f += size_t(colsum_parts(n, hp.target_vocabulary_size)) * hp.target_vocabulary_size + 64;
+    red_capacity = f + 4096;
+  }
   emb_scratch_bytes = embed_bwd_scratch_bytes(int(N));
   size_t bytes = 0;
   auto need = [&](size_t count, size_t elt) { bytes += align_up(count * elt, 256); };
   // encoder: x (L+1), qkv, ctx, z1, o1, h, z2, lse, 4 stats
   need(nd * (L + 1), 2);
-  for (int l = 0; l < L; ++l) { need(3 * nd, 2); need(nd, 2); need(nd, 2); need(nd, 2); need(nff, 2); need(nd, 2); need(N * H, 4); need(4 * N, 4); }
+  for (int l = 0; l < L; ++l) { need(3 * nd, 2); need(nd, 2); need(nd, 2); need(nd, 2); need(nff, 2); need(nd, 2); need(2 * N * H, 4); need(4 * N, 4); }
   // decoder: x (L+1), qkv, ctx1, z1, o1, q2, ctx2, z2, o2, h, z3, lse1, lse2, 6 stats
   need(nd * (L + 1), 2);
-  for (int l = 0; l < L; ++l) { need(3 * nd, 2); for (int i = 0; i < 8; ++i) need(nd, 2); need(nff, 2); need(2 * N * H, 4); need(6 * N, 4); }
+  for (int l = 0; l < L; ++l) { need(3 * nd, 2); for (int i = 0; i < 8; ++i) need(nd, 2); need(nff, 2); need(4 * N * H, 4); need(6 * N, 4); }
   need(N * size_t(L) * 2 * d, 2); need(N * size_t(L) * 2 * d, 2);   // kv_all, dkv_all
   need(N * size_t(vt_ld), 2);                                       // logits / dlogits
   for (int i = 0; i < 5; ++i) need(nd, 2);                          // dA dB dz dctx dq2
@@ -256,7 +264,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   need(N * H, 4);                                                   // delta
   for (int i = 0; i < 4; ++i) need(N + 64, 8);                      // inp, target, tgt_in, labels
   need(N, 4); need(N, 4);                                           // row_loss, row_correct
-  need(ln_scr + 64, 4); need(emb_scratch_bytes, 1);
+  need(red_capacity, 4); need(emb_scratch_bytes, 1);
   need(size_t(hp.maximum_input_length) * d, 4); need(size_t(hp.maximum_target_length) * d, 4);
   need(1024, 1);
   arena_size = bytes + (1 << 20);
@@ -270,7 +278,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
     EncAct& a = ea[l];
     B200XF_TRY(arena_alloc(&a.qkv, 3 * nd)); B200XF_TRY(arena_alloc(&a.ctx, nd)); B200XF_TRY(arena_alloc(&a.z1, nd));
     B200XF_TRY(arena_alloc(&a.o1, nd)); B200XF_TRY(arena_alloc(&a.h, nff)); B200XF_TRY(arena_alloc(&a.z2, nd));
-    B200XF_TRY(arena_alloc(&a.lse, N * H)); B200XF_TRY(arena_alloc(&a.stats, 4 * N));
+    B200XF_TRY(arena_alloc(&a.lse, 2 * N * H)); B200XF_TRY(arena_alloc(&a.stats, 4 * N));
   }
   B200XF_TRY(arena_alloc(&dec_x, nd * (L + 1)));
   da.resize(L);
@@ -279,7 +287,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
     B200XF_TRY(arena_alloc(&a.qkv, 3 * nd)); B200XF_TRY(arena_alloc(&a.ctx1, nd)); B200XF_TRY(arena_alloc(&a.z1, nd));
     B200XF_TRY(arena_alloc(&a.o1, nd)); B200XF_TRY(arena_alloc(&a.q2, nd)); B200XF_TRY(arena_alloc(&a.ctx2, nd));
     B200XF_TRY(arena_alloc(&a.z2, nd)); B200XF_TRY(arena_alloc(&a.o2, nd)); B200XF_TRY(arena_alloc(&a.z3, nd));
-    B200XF_TRY(arena_alloc(&a.h, nff)); B200XF_TRY(arena_alloc(&a.lse1, N * H)); B200XF_TRY(arena_alloc(&a.lse2, N * H));
+    B200XF_TRY(arena_alloc(&a.h, nff)); B200XF_TRY(arena_alloc(&a.lse1, 2 * N * H)); B200XF_TRY(arena_alloc(&a.lse2, 2 * N * H));
     B200XF_TRY(arena_alloc(&a.stats, 6 * N));
   }
   B200XF_TRY(arena_alloc(&kv, N * size_t(L) * 2 * d)); B200XF_TRY(arena_alloc(&dkv, N * size_t(L) * 2 * d));
@@ -291,7 +299,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   B200XF_TRY(arena_alloc(&tok_inp, N + 64)); B200XF_TRY(arena_alloc(&tok_target, N + 64));
   B200XF_TRY(arena_alloc(&tok_tgt_in, N + 64)); B200XF_TRY(arena_alloc(&tok_labels, N + 64));
   B200XF_TRY(arena_alloc(&row_loss, N)); B200XF_TRY(arena_alloc(&row_correct, N));
-  B200XF_TRY(arena_alloc(&ln_scratch, ln_scr + 64));
+  B200XF_TRY(arena_alloc(&red_scratch, red_capacity));
   B200XF_TRY(arena_alloc(&emb_scratch, emb_scratch_bytes));
   B200XF_TRY(arena_alloc(&pe_in, size_t(hp.maximum_input_length) * d));
   B200XF_TRY(arena_alloc(&pe_tgt, size_t(hp.maximum_target_length) * d));
@@ -299,7 +307,6 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   B200XF_TRY(arena_alloc(&small, 1024));
   iterations_dev = reinterpret_cast<long long*>(small);
   nonpad_count = reinterpret_cast<int*>(small + 64);
-  ln_counter = reinterpret_cast<unsigned*>(small + 128);
   metrics = reinterpret_cast<float*>(small + 256);      // 3 local + 3 reduced
 
   {
@@ -484,11 +491,42 @@ int Context::forward(const long long* inp, const long long* tgt_in, int B, int S
 }
 
 // ------------------------------------------------------------------------------------ backward
+float* Context::red_alloc(size_t floats) {
+  floats = (floats + 63) / 64 * 64;
+  if (red_used + floats > red_capacity) return nullptr;
+  float* p = red_scratch + red_used;
+  red_used += floats;
+  return p;
+}
+
 int Context::ln_bwd(const bf16* dy, const bf16* z, const float* st_mean, const float* st_rstd, const LnP& p, size_t dcol_off,
                     int rows) {
   const int d = hp.embedding_size;
-  return layernorm_bwd(dy, z, st_mean, st_rstd, params + p.g, dz, grads + p.g, grads + p.b, grads + dcol_off, rows, d,
-                       ln_scratch, ln_counter, stream);
+  const int n = ln_bwd_parts(rows);
+  float* part = red_alloc(size_t(n) * 3 * d);
+  if (!part) return set_error("reduction scratch exhausted");
+  B200XF_TRY(layernorm_bwd_partial(dy, z, st_mean, st_rstd, params + p.g, dz, rows, d, part, stream));
+  red_jobs.push_back({part, grads + p.g, n, d, 3 * d});
+  red_jobs.push_back({part + d, grads + p.b, n, d, 3 * d});
+  red_jobs.push_back({part + 2 * d, grads + dcol_off, n, d, 3 * d});
+  return 0;
+}
+
+int Context::colsum(const bf16* x, int ld, int rows, int cols, size_t dst_off) {
+  const int n = colsum_parts(rows, cols);
+  float* part = red_alloc(size_t(n) * cols);
+  if (!part) return set_error("reduction scratch exhausted");
+  B200XF_TRY(colsum_partial(x, ld, rows, cols, part, stream));
+  red_jobs.push_back({part, grads + dst_off, n, cols, cols});
+  return 0;
+}
+
+// One launch sums every pending set of column-sum partials (bias / gamma / beta gradients) into the flat gradient.
+int Context::flush_reductions() {
+  if (red_jobs.empty()) return 0;
+  B200XF_TRY(reduce_partials(red_jobs.data(), int(red_jobs.size()), stream));
+  red_jobs.clear();
+  return 0;
 }
 
 int Context::backward(const long long* inp, const long long* tgt_in, int B, int S, int T) {
@@ -499,10 +537,11 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
   if (!grads_clean) B200XF_CUDA(cudaMemsetAsync(grads, 0, total_params * sizeof(float), stream));
   grads_clean = false;
   next_section = 0;
+  red_used = 0; red_jobs.clear();
 
   const bf16* dec_out = dec_x + size_t(L) * cap;
   B200XF_TRY(dense_wgrad(dec_out, logits, Nt, final_layer));
-  B200XF_TRY(colsum_bf16(logits, final_layer.ld, Nt, final_layer.N, grads + final_layer.b, 0, stream));
+  B200XF_TRY(colsum(logits, final_layer.ld, Nt, final_layer.N, final_layer.b));
   bf16* cur = dA; bf16* other = dB;
   B200XF_TRY(dense_dgrad(logits, Nt, final_layer, cur, nullptr, 0));
   B200XF_TRY(section_done());
@@ -515,7 +554,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     B200XF_TRY(ln_bwd(cur, a.z3, st + 4 * Nt, st + 5 * Nt, w.ln3, w.f2.b, Nt));
     B200XF_TRY(dense_wgrad(a.h, dz, Nt, w.f2));
     B200XF_TRY(dense_dgrad(dz, Nt, w.f2, dh, a.h, 2));
-    B200XF_TRY(colsum_bf16(dh, w.f1.ld, Nt, w.f1.N, grads + w.f1.b, 0, stream));
+    B200XF_TRY(colsum(dh, w.f1.ld, Nt, w.f1.N, w.f1.b));
     B200XF_TRY(dense_wgrad(a.o2, dh, Nt, w.f1));
     B200XF_TRY(dense_dgrad(dh, Nt, w.f1, other, dz, 1));
     std::swap(cur, other);
@@ -530,7 +569,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     c2.d_o = dctx; c2.lddo = d; c2.dq = dq2; c2.lddq = d;
     c2.dk_out = dkv + size_t(l) * 2 * d; c2.dv_out = dkv + size_t(l) * 2 * d + d; c2.lddk = c2.lddv = kv_all.ld; c2.delta = delta;
     B200XF_TRY(attention_bwd(c2, stream));
-    B200XF_TRY(colsum_bf16(dq2, d, Nt, d, grads + w.q2.b, 0, stream));
+    B200XF_TRY(colsum(dq2, d, Nt, d, w.q2.b));
     B200XF_TRY(dense_wgrad(a.o1, dq2, Nt, w.q2));
     B200XF_TRY(dense_dgrad(dq2, Nt, w.q2, other, dz, 1));
     std::swap(cur, other);
@@ -545,7 +584,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     s1.d_o = dctx; s1.lddo = d; s1.dq = dqkv; s1.dk_out = dqkv + d; s1.dv_out = dqkv + 2 * d; s1.lddq = s1.lddk = s1.lddv = 3 * d;
     s1.delta = delta;
     B200XF_TRY(attention_bwd(s1, stream));
-    B200XF_TRY(colsum_bf16(dqkv, 3 * d, Nt, 3 * d, grads + w.qkv1.b, 0, stream));
+    B200XF_TRY(colsum(dqkv, 3 * d, Nt, 3 * d, w.qkv1.b));
     B200XF_TRY(dense_wgrad(x, dqkv, Nt, w.qkv1));
     B200XF_TRY(dense_dgrad(dqkv, Nt, w.qkv1, other, dz, 1));
     std::swap(cur, other);
@@ -553,7 +592,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
   }
   B200XF_TRY(embed_bwd(tgt_in, cur, grads + dec_emb, hp.target_vocabulary_size, Nt, d, emb_scratch, emb_scratch_bytes, stream));
   const bf16* enc_out = enc_x + size_t(L) * cap;
-  B200XF_TRY(colsum_bf16(dkv, kv_all.ld, Ns, kv_all.N, grads + kv_all.b, 0, stream));
+  B200XF_TRY(colsum(dkv, kv_all.ld, Ns, kv_all.N, kv_all.b));
   B200XF_TRY(dense_wgrad(enc_out, dkv, Ns, kv_all));
   B200XF_TRY(dense_dgrad(dkv, Ns, kv_all, cur, nullptr, 0));
   B200XF_TRY(section_done());
@@ -565,7 +604,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     B200XF_TRY(ln_bwd(cur, a.z2, st + 2 * Ns, st + 3 * Ns, w.ln2, w.f2.b, Ns));
     B200XF_TRY(dense_wgrad(a.h, dz, Ns, w.f2));
     B200XF_TRY(dense_dgrad(dz, Ns, w.f2, dh, a.h, 2));
-    B200XF_TRY(colsum_bf16(dh, w.f1.ld, Ns, w.f1.N, grads + w.f1.b, 0, stream));
+    B200XF_TRY(colsum(dh, w.f1.ld, Ns, w.f1.N, w.f1.b));
     B200XF_TRY(dense_wgrad(a.o1, dh, Ns, w.f1));
     B200XF_TRY(dense_dgrad(dh, Ns, w.f1, other, dz, 1));
     std::swap(cur, other);
@@ -579,7 +618,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     at.d_o = dctx; at.lddo = d; at.dq = dqkv; at.dk_out = dqkv + d; at.dv_out = dqkv + 2 * d; at.lddq = at.lddk = at.lddv = 3 * d;
     at.delta = delta;
     B200XF_TRY(attention_bwd(at, stream));
-    B200XF_TRY(colsum_bf16(dqkv, 3 * d, Ns, 3 * d, grads + w.qkv.b, 0, stream));
+    B200XF_TRY(colsum(dqkv, 3 * d, Ns, 3 * d, w.qkv.b));
     B200XF_TRY(dense_wgrad(x, dqkv, Ns, w.qkv));
     B200XF_TRY(dense_dgrad(dqkv, Ns, w.qkv, other, dz, 1));
     std::swap(cur, other);
@@ -587,6 +626,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
   }
   B200XF_TRY(embed_bwd(inp, cur, grads + enc_emb, hp.input_vocabulary_size, Ns, d, emb_scratch, emb_scratch_bytes, stream));
   B200XF_TRY(section_done());
+  B200XF_TRY(flush_reductions());
   return 0;
 }
 
@@ -600,6 +640,7 @@ int Context::section_done() {
   const size_t end = sections[idx].second;
   const bool last = (idx + 1 == sections.size());
   if (!last && (end - bucket_begin) * sizeof(float) < bucket_bytes) return 0;
+  B200XF_TRY(flush_reductions());
   B200XF_CUDA(cudaEventRecord(ev_ready, stream));
   B200XF_CUDA(cudaStreamWaitEvent(comm_stream, ev_ready, 0));
   B200XF_TRY(allreduce(grads + bucket_begin, end - bucket_begin, comm_stream));

@@ -49,9 +49,10 @@ struct Context {
   bf16 *enc_x = nullptr, *dec_x = nullptr, *kv = nullptr, *dkv = nullptr, *logits = nullptr;
   std::vector<EncAct> ea; std::vector<DecAct> da;
   bf16 *dA = nullptr, *dB = nullptr, *dz = nullptr, *dctx = nullptr, *dq2 = nullptr, *dh = nullptr, *dqkv = nullptr;
-  float *delta = nullptr, *row_loss = nullptr, *ln_scratch = nullptr, *pe_in = nullptr, *pe_tgt = nullptr, *metrics = nullptr;
+  float *delta = nullptr, *row_loss = nullptr, *red_scratch = nullptr, *pe_in = nullptr, *pe_tgt = nullptr, *metrics = nullptr;
   int *row_correct = nullptr, *nonpad_count = nullptr;
-  unsigned* ln_counter = nullptr;
+  size_t red_capacity = 0, red_used = 0;
+  std::vector<ReduceJob> red_jobs;
   long long *tok_inp = nullptr, *tok_target = nullptr, *tok_tgt_in = nullptr, *tok_labels = nullptr;
   char* emb_scratch = nullptr; size_t emb_scratch_bytes = 0;
   float* host_out = nullptr;
@@ -82,6 +83,9 @@ struct Context {
   int dense_dgrad(const bf16* dy, int M, const Dense& p, bf16* dx, const bf16* resid, int resid_op);
   int dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p);
   int ln_bwd(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const LnP& p, size_t dcol_off, int rows);
+  int colsum(const bf16* x, int ld, int rows, int cols, size_t dst_off);
+  float* red_alloc(size_t floats);
+  int flush_reductions();
   int check_shapes(int B, int S, int T);
   int forward(const long long* inp, const long long* tgt_in, int B, int S, int T, float* logits_f32);
   int backward(const long long* inp, const long long* tgt_in, int B, int S, int T);

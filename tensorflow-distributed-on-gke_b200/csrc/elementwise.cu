@@ -93,17 +93,15 @@ ln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ resid, const 
 }
 
 // Backward: dz = rstd * (g - mean(g) - xhat * mean(g*xhat)),  g = dy * gamma.
-// Column sums (dgamma, dbeta, colsum(dz)) are accumulated per lane across the block's rows, reduced
-// across the block's warps in shared memory in a fixed order, written as per-block partials, and summed
-// by the last block to finish (threadfence + counter) — deterministic, no float atomics.
+// Column sums (dgamma, dbeta, colsum(dz)) are accumulated per lane across the block's rows, reduced across the
+// block's warps in shared memory in a fixed order and written as per-block partials [block][3][d]; a batched
+// reduce_partials launch sums them later in a fixed order (deterministic, no float atomics).
 template <int CH>
 __global__ void __launch_bounds__(kLnWarps * 32)
 ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const float* __restrict__ mean_in,
-              const float* __restrict__ rstd_in, const float* __restrict__ gamma, bf16* __restrict__ dz,
-              float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dcol, int rows, int d,
-              float* __restrict__ scratch, unsigned* __restrict__ counter) {
+              const float* __restrict__ rstd_in, const float* __restrict__ gamma, bf16* __restrict__ dz, int rows, int d,
+              float* __restrict__ partials) {
   extern __shared__ float red[];  // [3][d]
-  __shared__ bool is_last;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float gam[CH][8];
   float acc_g[CH][8], acc_b[CH][8], acc_c[CH][8];
@@ -163,25 +161,40 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
     }
     __syncthreads();
   }
-  float* mine = scratch + size_t(blockIdx.x) * 3 * d;
+  float* mine = partials + size_t(blockIdx.x) * 3 * d;
   for (int i = threadIdx.x; i < 3 * d; i += blockDim.x) mine[i] = red[i];
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) is_last = (atomicAdd(counter, 1u) == gridDim.x - 1);
-  __syncthreads();
-  if (!is_last) return;
-  __threadfence();
-  for (int i = threadIdx.x; i < 3 * d; i += blockDim.x) {
-    float s = 0.f;
-    for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(scratch + size_t(b) * 3 * d + i);
-    if (i < d) dgamma[i] = s;
-    else if (i < 2 * d) dbeta[i - d] = s;
-    else if (dcol) dcol[i - 2 * d] = s;
-  }
-  if (threadIdx.x == 0) *counter = 0u;  // leave the counter ready for the next call
 }
 
-int ln_bwd_grid(int rows) { return max(1, min((rows + kLnWarps - 1) / kLnWarps, 2 * num_sms())); }
+// dst[c] = sum_p src[p * stride + c] for a batch of jobs; block = 32 columns x 8 slices of the partials.
+struct ReduceJobTable {
+  static constexpr int kMax = 96;
+  const float* src[kMax]; float* dst[kMax];
+  int nparts[kMax], cols[kMax], stride[kMax], first_block[kMax + 1];
+  int njobs;
+};
+__global__ void __launch_bounds__(256)
+reduce_partials_kernel(const __grid_constant__ ReduceJobTable t) {
+  __shared__ float red[8][33];
+  int j = 0;
+  while (j + 1 < t.njobs && int(blockIdx.x) >= t.first_block[j + 1]) ++j;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int col = (blockIdx.x - t.first_block[j]) * 32 + tx;
+  float acc = 0.f;
+  if (col < t.cols[j]) {
+    const float* s = t.src[j] + col;
+    const int n = t.nparts[j], st = t.stride[j];
+#pragma unroll 4
+    for (int p = ty; p < n; p += 8) acc += __ldcg(s + size_t(p) * st);
+  }
+  red[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0 && col < t.cols[j]) {
+    float v = red[0][tx];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) v += red[i][tx];
+    t.dst[j][col] = v;
+  }
+}
 
 }  // namespace
 
@@ -199,22 +212,51 @@ int layernorm_fwd(const bf16* x, const bf16* resid, const float* gamma, const fl
   return 0;
 }
 
-size_t ln_bwd_scratch_floats(int rows, int d) { return size_t(ln_bwd_grid(rows)) * 3 * d; }
+int ln_bwd_parts(int rows) { return std::max(1, std::min((rows + kLnWarps - 1) / kLnWarps, num_sms())); }
+size_t ln_bwd_scratch_floats(int rows, int d) { return size_t(ln_bwd_parts(rows)) * 3 * d; }
 
-int layernorm_bwd(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const float* gamma, bf16* dz,
-                  float* dgamma, float* dbeta, float* dcol, int rows, int d, float* scratch, unsigned* counter,
-                  cudaStream_t stream) {
+int layernorm_bwd_partial(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const float* gamma, bf16* dz, int rows,
+                          int d, float* partials, cudaStream_t stream) {
   if (d % 8 || d > 2048) return set_error("layernorm: d=%d must be a multiple of 8 and <= 2048", d);
-  if (rows <= 0) return 0;
-  const int grid = ln_bwd_grid(rows);
+  if (rows <= 0) return set_error("layernorm_bwd: no rows");
+  const int grid = ln_bwd_parts(rows);
   const int ch = (d + 255) / 256;
   const size_t smem = size_t(3) * d * sizeof(float);
-#define LN_BWD(CH) ln_bwd_kernel<CH><<<grid, kLnWarps * 32, smem, stream>>>(dy, z, mean, rstd, gamma, dz, dgamma, dbeta, dcol, rows, d, scratch, counter)
+#define LN_BWD(CH) ln_bwd_kernel<CH><<<grid, kLnWarps * 32, smem, stream>>>(dy, z, mean, rstd, gamma, dz, rows, d, partials)
   if (ch <= 1) LN_BWD(1); else if (ch <= 2) LN_BWD(2); else if (ch <= 4) LN_BWD(4); else LN_BWD(8);
 #undef LN_BWD
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;
+}
+
+int reduce_partials(const ReduceJob* jobs, int njobs, cudaStream_t stream) {
+  for (int base = 0; base < njobs; base += ReduceJobTable::kMax) {
+    ReduceJobTable t;
+    t.njobs = std::min(ReduceJobTable::kMax, njobs - base);
+    int blocks = 0;
+    for (int i = 0; i < t.njobs; ++i) {
+      const ReduceJob& j = jobs[base + i];
+      t.src[i] = j.src; t.dst[i] = j.dst; t.nparts[i] = j.nparts; t.cols[i] = j.cols; t.stride[i] = j.stride;
+      t.first_block[i] = blocks;
+      blocks += (j.cols + 31) / 32;
+    }
+    t.first_block[t.njobs] = blocks;
+    if (blocks == 0) continue;
+    reduce_partials_kernel<<<blocks, 256, 0, stream>>>(t);
+    B200XF_CUDA(cudaGetLastError());
+    count_launch();
+  }
+  return 0;
+}
+
+int layernorm_bwd(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const float* gamma, bf16* dz,
+                  float* dgamma, float* dbeta, float* dcol, int rows, int d, float* scratch, cudaStream_t stream) {
+  if (rows <= 0) return 0;
+  B200XF_TRY(layernorm_bwd_partial(dy, z, mean, rstd, gamma, dz, rows, d, scratch, stream));
+  const int n = ln_bwd_parts(rows);
+  ReduceJob jobs[3] = {{scratch, dgamma, n, d, 3 * d}, {scratch + d, dbeta, n, d, 3 * d}, {scratch + 2 * d, dcol, n, d, 3 * d}};
+  return reduce_partials(jobs, dcol ? 3 : 2, stream);
 }
 
 // ============================================================================ embedding + PE
@@ -232,8 +274,9 @@ __global__ void embed_fwd_kernel(const long long* __restrict__ tokens, const flo
     float4 e = ok ? __ldg(reinterpret_cast<const float4*>(row + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
     const float4 q = __ldg(reinterpret_cast<const float4*>(p + c));
     uint2 u;
-    u.x = ptx::pack_bf16x2(e.x * scale + q.x, e.y * scale + q.y);
-    u.y = ptx::pack_bf16x2(e.z * scale + q.z, e.w * scale + q.w);
+    // two separately rounded fp32 ops, as `x *= sqrt(d); x += pe` in the reference (no FMA contraction)
+    u.x = ptx::pack_bf16x2(__fadd_rn(__fmul_rn(e.x, scale), q.x), __fadd_rn(__fmul_rn(e.y, scale), q.y));
+    u.y = ptx::pack_bf16x2(__fadd_rn(__fmul_rn(e.z, scale), q.z), __fadd_rn(__fmul_rn(e.w, scale), q.w));
     *reinterpret_cast<uint2*>(out + size_t(n) * d + c) = u;
   }
 }
@@ -497,10 +540,11 @@ adam_kernel(float4* __restrict__ w, float4* __restrict__ g, float4* __restrict__
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x) {
     float4 W = w[i], M = m[i], V = v[i];
     const float4 G = g[i];
-#define ADAM1(c)                                  \
-    M.c += (G.c - M.c) * c1;                      \
-    V.c += (G.c * G.c - V.c) * c2;                \
-    W.c -= (M.c * alpha) / (sqrtf(V.c) + h.eps);
+    // each operation rounded separately, exactly as the expression is written (no FMA contraction)
+#define ADAM1(c)                                                                              \
+    M.c = __fadd_rn(M.c, __fmul_rn(__fsub_rn(G.c, M.c), c1));                                 \
+    V.c = __fadd_rn(V.c, __fmul_rn(__fsub_rn(__fmul_rn(G.c, G.c), V.c), c2));                 \
+    W.c = __fsub_rn(W.c, __fdiv_rn(__fmul_rn(M.c, alpha), __fadd_rn(__fsqrt_rn(V.c), h.eps)));
     ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
 #undef ADAM1
     w[i] = W; m[i] = M; v[i] = V;
@@ -533,36 +577,36 @@ int increment_counter(long long* iterations_dev, cudaStream_t stream) {
 
 // ============================================================================ helpers
 namespace {
-// out[c] (+)= sum_r x[r][c]; block = 16 column groups (4 bf16 each) x 16 row phases.
+// partial[strip][c] = sum over the strip's rows of x[r][c]; block = 8 column groups (8 bf16 each) x 32 row phases.
 __global__ void __launch_bounds__(256)
-colsum_kernel(const bf16* __restrict__ x, int ld, int rows, int cols, float* __restrict__ out, int accumulate) {
-  __shared__ float4 red[16][16];
-  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-  const int col = blockIdx.x * 64 + tx * 4;
-  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+colsum_partial_kernel(const bf16* __restrict__ x, int ld, int rows, int cols, int rows_per_strip, float* __restrict__ partials) {
+  __shared__ float red[32][65];
+  const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
+  const int col = blockIdx.x * 64 + tx * 8;
+  const int r0 = blockIdx.y * rows_per_strip, r1 = min(rows, r0 + rows_per_strip);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (col < cols) {
-    const bool fullv = col + 4 <= cols;
+    if (col + 8 <= cols) {
 #pragma unroll 4
-    for (int r = ty; r < rows; r += 16) {
-      const bf16* p = x + size_t(r) * ld + col;
-      if (fullv) {
-        const uint2 u = *reinterpret_cast<const uint2*>(p);
-        acc.x += ptx::bf16_lo(u.x); acc.y += ptx::bf16_hi(u.x); acc.z += ptx::bf16_lo(u.y); acc.w += ptx::bf16_hi(u.y);
-      } else {
-        acc.x += __bfloat162float(p[0]);
-        if (col + 1 < cols) acc.y += __bfloat162float(p[1]);
-        if (col + 2 < cols) acc.z += __bfloat162float(p[2]);
+      for (int r = r0 + ty; r < r1; r += 32) {
+        float f[8];
+        unpack8(*reinterpret_cast<const uint4*>(x + size_t(r) * ld + col), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
       }
+    } else {
+      for (int r = r0 + ty; r < r1; r += 32)
+        for (int j = 0; j < 8 && col + j < cols; ++j) acc[j] += __bfloat162float(x[size_t(r) * ld + col + j]);
     }
   }
-  red[ty][tx] = acc;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[ty][tx * 8 + j] = acc[j];
   __syncthreads();
-  if (ty == 0 && col < cols) {
-    float4 s = red[0][tx];
-    for (int i = 1; i < 16; ++i) { s.x += red[i][tx].x; s.y += red[i][tx].y; s.z += red[i][tx].z; s.w += red[i][tx].w; }
-    const float v[4] = {s.x, s.y, s.z, s.w};
-    for (int j = 0; j < 4; ++j)
-      if (col + j < cols) out[col + j] = accumulate ? out[col + j] + v[j] : v[j];
+  if (threadIdx.x < 64 && blockIdx.x * 64 + threadIdx.x < cols) {
+    float v = 0.f;
+#pragma unroll 8
+    for (int i = 0; i < 32; ++i) v += red[i][threadIdx.x];
+    partials[size_t(blockIdx.y) * cols + blockIdx.x * 64 + threadIdx.x] = v;
   }
 }
 
@@ -583,10 +627,18 @@ __global__ void cast_back_kernel(const bf16* __restrict__ in, int ldi, float* __
 }
 }  // namespace
 
-int colsum_bf16(const bf16* x, int ld, int rows, int cols, float* out, int accumulate, cudaStream_t stream) {
-  if (ld % 4) return set_error("colsum: ld=%d must be a multiple of 4", ld);
-  if (cols <= 0) return 0;
-  colsum_kernel<<<(cols + 63) / 64, 256, 0, stream>>>(x, ld, rows, cols, out, accumulate);
+int colsum_parts(int rows, int cols) {
+  const int colblocks = (cols + 63) / 64;
+  const int want = (2 * num_sms() + colblocks - 1) / colblocks;
+  return std::max(1, std::min(want, (rows + 127) / 128));
+}
+
+int colsum_partial(const bf16* x, int ld, int rows, int cols, float* partials, cudaStream_t stream) {
+  if (ld % 8 || (reinterpret_cast<uintptr_t>(x) & 15)) return set_error("colsum: x must be 16-byte aligned with ld %% 8 == 0");
+  if (cols <= 0 || rows <= 0) return set_error("colsum: empty problem");
+  const int strips = colsum_parts(rows, cols);
+  const int rps = (rows + strips - 1) / strips;
+  colsum_partial_kernel<<<dim3((cols + 63) / 64, strips), 256, 0, stream>>>(x, ld, rows, cols, rps, partials);
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;

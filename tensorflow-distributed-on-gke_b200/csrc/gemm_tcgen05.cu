@@ -15,6 +15,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <map>
 #include <mutex>
@@ -45,7 +46,7 @@ struct Cfg {
 struct GemmParams {
   int M, N, K;
   int tiles_m, tiles_n, splits, kb_per_split;
-  void* d; int ldd; int d_fp32; int accumulate;
+  void* d; int ldd; int d_fp32; int accumulate; int d_vec;  // d_vec: rows are 16-byte aligned -> vector stores
   const float* bias; int relu;
   const __nv_bfloat16* resid; int ldr; int resid_op;  // 0 none, 1 add, 2 relu-mask
   float alpha;
@@ -214,7 +215,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             float* dp = reinterpret_cast<float*>(p.d) + size_t(row) * p.ldd + col0;
 #pragma unroll
             for (int g = 0; g < 8; ++g) {
-              if (col0 + g * 4 + 4 <= p.N) {
+              if (p.d_vec && col0 + g * 4 + 4 <= p.N) {
                 if (p.accumulate) ptx::red_add_v4(dp + g * 4, f[g * 4], f[g * 4 + 1], f[g * 4 + 2], f[g * 4 + 3]);
                 else *reinterpret_cast<float4*>(dp + g * 4) = make_float4(f[g * 4], f[g * 4 + 1], f[g * 4 + 2], f[g * 4 + 3]);
               } else {
@@ -229,7 +230,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             __nv_bfloat16* dp = reinterpret_cast<__nv_bfloat16*>(p.d) + size_t(row) * p.ldd + col0;
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
-              if (col0 + g * 8 + 8 <= p.N) {
+              if (p.d_vec && col0 + g * 8 + 8 <= p.N) {
                 uint4 u;
                 u.x = ptx::pack_bf16x2(f[g * 8], f[g * 8 + 1]); u.y = ptx::pack_bf16x2(f[g * 8 + 2], f[g * 8 + 3]);
                 u.z = ptx::pack_bf16x2(f[g * 8 + 4], f[g * 8 + 5]); u.w = ptx::pack_bf16x2(f[g * 8 + 6], f[g * 8 + 7]);
@@ -337,36 +338,45 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   if (a.accumulate && !a.d_fp32) return set_error("gemm: accumulate requires fp32 output");
   const int nsm = num_sms();
   const int tiles_m = (a.M + BM - 1) / BM;
-  int bn = a.force_bn;
+  const int total_kb = (a.K + BK - 1) / BK;
+  // Tile width: model each CTA's time as (k-blocks it runs) x (BN + 64 columns of fixed per-k-block cost) plus a per-tile
+  // epilogue, over the waves the grid needs; split-K (fp32 atomic accumulate only) can fill idle SMs when tiles are few.
+  auto plan = [&](int cand, int* splits_out) {
+    const long tiles = long(tiles_m) * ((a.N + cand - 1) / cand);
+    int sp = 1;
+    if (a.accumulate) {
+      sp = a.split_k > 0 ? a.split_k : int(std::max<long>(1, std::min<long>(nsm / tiles, total_kb / 4)));
+      sp = std::max(1, std::min(sp, total_kb));
+    }
+    const int kb_per = (total_kb + sp - 1) / sp;
+    sp = (total_kb + kb_per - 1) / kb_per;
+    *splits_out = sp;
+    const long ctas = tiles * sp;
+    const long waves = (ctas + nsm - 1) / nsm;
+    return waves * (long(kb_per) * (cand + 64) + 4L * cand);
+  };
+  int bn = a.force_bn, splits = 1;
   if (bn == 0) {
     long best = -1;
     for (int cand : {256, 128, 64}) {
       if (cand > 64 && cand / 2 >= a.N) continue;  // do not waste more than half a tile
-      const long tiles = long(tiles_m) * ((a.N + cand - 1) / cand);
-      const long cost = ((tiles + nsm - 1) / nsm) * (cand + 64);
+      int sp;
+      const long cost = plan(cand, &sp);
       if (best < 0 || cost < best) { best = cost; bn = cand; }
     }
   }
   if (bn != 64 && bn != 128 && bn != 256) return set_error("gemm: unsupported BN %d", bn);
   const int tiles_n = (a.N + bn - 1) / bn;
-  const int total_kb = (a.K + BK - 1) / BK;
-  int splits = 1;
-  if (a.accumulate) {
-    splits = a.split_k;
-    if (splits <= 0) {
-      const int tiles = tiles_m * tiles_n;
-      splits = 1;
-      if (tiles * 2 <= nsm) splits = min(nsm / tiles, max(1, total_kb / 4));
-    }
-    splits = max(1, min(splits, total_kb));
-  }
-  int kb_per = (total_kb + splits - 1) / splits;
-  splits = (total_kb + kb_per - 1) / kb_per;
+  plan(bn, &splits);
+  const int kb_per = (total_kb + splits - 1) / splits;
 
   GemmParams p;
   p.M = a.M; p.N = a.N; p.K = a.K;
   p.tiles_m = tiles_m; p.tiles_n = tiles_n; p.splits = splits; p.kb_per_split = kb_per;
   p.d = a.d; p.ldd = a.ldd; p.d_fp32 = a.d_fp32; p.accumulate = a.accumulate;
+  p.d_vec = ((reinterpret_cast<uintptr_t>(a.d) & 15) == 0) && (a.ldd % (a.d_fp32 ? 4 : 8) == 0);
+  if (a.bias && (reinterpret_cast<uintptr_t>(a.bias) & 15)) return set_error("gemm: bias must be 16-byte aligned");
+  if (a.resid && ((reinterpret_cast<uintptr_t>(a.resid) & 15) || a.ldr % 8)) return set_error("gemm: resid must be 16-byte aligned with ldr %% 8 == 0");
   p.bias = a.bias; p.relu = a.relu;
   p.resid = reinterpret_cast<const __nv_bfloat16*>(a.resid); p.ldr = a.ldr; p.resid_op = a.resid ? a.resid_op : 0;
   p.alpha = a.alpha;

@@ -51,7 +51,7 @@ struct AttnArgs {
   const bf16* k = nullptr; int ldk = 0;   // [B*Sk, ldk]
   const bf16* v = nullptr; int ldv = 0;
   bf16* o = nullptr; int ldo = 0;         // [B*Sq, ldo]
-  float* lse = nullptr;                   // [B,H,Sq] log2-domain logsumexp of scaled+masked scores
+  float* lse = nullptr;                   // [B,H,Sq,2] {row max, log2(row sum)} of the scaled+masked scores, log2 domain
   const long long* key_tokens = nullptr;  // [B,Sk] int64; key j masked iff token == 0
   int causal = 0;                         // additionally mask j > i
   int B = 0, H = 0, Sq = 0, Sk = 0, dk = 0;
@@ -69,12 +69,18 @@ int attention_bwd(const AttnArgs& a, cudaStream_t stream);
 // ---- LayerNorm (+ optional residual add) fwd / bwd (transformer_model.py:187-188,198,204)
 int layernorm_fwd(const bf16* x, const bf16* resid, const float* gamma, const float* beta, bf16* y, bf16* z_out,
                   float* mean, float* rstd, int rows, int d, float eps, cudaStream_t stream);
-// dz = LN'(dy); dgamma/dbeta (+= over rows, overwritten), dcol = colsum(dz) (bias grad of the producing GEMM, may be null).
-// scratch: floats [ln_bwd_scratch_floats(rows,d)] + one unsigned counter that must be zero on entry (left zero on exit).
+// Column sums are produced as per-block partials and summed later by one batched launch (reduce_partials), in a
+// fixed order: deterministic, and the many small reductions of a backward pass share one launch.
+struct ReduceJob { const float* src; float* dst; int nparts; int cols; int stride; };  // dst[c] = sum_p src[p*stride + c]
+int reduce_partials(const ReduceJob* jobs, int njobs, cudaStream_t stream);
+// dz = LN'(dy); partials [ln_bwd_parts(rows)][3][d] = per-block sums of (dy*xhat, dy, dz) -> dgamma, dbeta, colsum(dz).
+int ln_bwd_parts(int rows);
 size_t ln_bwd_scratch_floats(int rows, int d);
+int layernorm_bwd_partial(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const float* gamma, bf16* dz,
+                          int rows, int d, float* partials, cudaStream_t stream);
+// convenience: partial + reduce; scratch holds ln_bwd_scratch_floats(rows, d) floats.  dcol may be null.
 int layernorm_bwd(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const float* gamma, bf16* dz,
-                  float* dgamma, float* dbeta, float* dcol, int rows, int d, float* scratch, unsigned* counter,
-                  cudaStream_t stream);
+                  float* dgamma, float* dbeta, float* dcol, int rows, int d, float* scratch, cudaStream_t stream);
 
 // ---- embedding * sqrt(d) + positional encoding (transformer_model.py:273-275,305-307)
 int embed_pe_fwd(const long long* tokens, const float* table, int vocab, const float* pe, bf16* out, int B, int S, int d,
@@ -101,7 +107,9 @@ int adam_step(float* w, float* g, float* m, float* v, bf16* w_bf16, size_t n, co
 int increment_counter(long long* iterations_dev, cudaStream_t stream);
 
 // ---- small helpers
-int colsum_bf16(const bf16* x, int ld, int rows, int cols, float* out, int accumulate, cudaStream_t stream);
+// partials [colsum_parts(rows, cols)][cols] of the column sums of a bf16 matrix
+int colsum_parts(int rows, int cols);
+int colsum_partial(const bf16* x, int ld, int rows, int cols, float* partials, cudaStream_t stream);
 int cast_f32_to_bf16(const float* in, bf16* out, size_t n, cudaStream_t stream);
 int cast_bf16_to_f32_2d(const bf16* in, int ldi, float* out, int ldo, int rows, int cols, cudaStream_t stream);
 

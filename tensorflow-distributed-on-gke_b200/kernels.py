@@ -49,7 +49,7 @@ def attention_fwd(q, k, v, key_tokens, causal, H):
     Sk = k.shape[1]
     dk = D // H
     o = torch.empty((B, Sq, D), device=q.device, dtype=torch.bfloat16)
-    lse = torch.empty((B, H, Sq), device=q.device, dtype=torch.float32)
+    lse = torch.empty((B, H, Sq, 2), device=q.device, dtype=torch.float32)
     check(lib.b200xf_attention_fwd(ptr(q), q.stride(1), ptr(k), k.stride(1), ptr(v), v.stride(1), ptr(o), o.stride(1), ptr(lse),
                                    ptr(key_tokens), int(causal), B, H, Sq, Sk, dk, stream_ptr()))
     return o, lse

