@@ -9,6 +9,9 @@
 //
 // Tensor-core path: mma.sync.m16n8k16 bf16 (fp32 accumulate) with ldmatrix operands; 64 query rows per
 // CTA (16 per warp) against 64-key tiles.
+#include <mutex>
+#include <set>
+
 #include "internal.h"
 #include "ptx.cuh"
 
@@ -53,6 +56,22 @@ __device__ __forceinline__ void load_tile(typename Smem<DK>::Tile& dst, const bf
     *reinterpret_cast<uint4*>(&dst[r][c]) = v;
   }
 }
+
+// Same, with cp.async (16-byte chunks, zero fill past the end): the copy overlaps whatever the CTA does next.
+template <int DK>
+__device__ __forceinline__ void load_tile_async(typename Smem<DK>::Tile& dst, const bf16* __restrict__ src, int ld, int row0,
+                                                int rows_total, int col0) {
+  constexpr int kChunks = DK / 8;
+  for (int i = threadIdx.x; i < kTile * kChunks; i += kWarps * 32) {
+    const int r = i / kChunks, c = (i % kChunks) * 8;
+    const bool ok = row0 + r < rows_total;
+    const bf16* g = src + size_t(ok ? row0 + r : 0) * ld + col0 + c;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(ptx::smem_u32(&dst[r][c])), "l"(g), "r"(ok ? 16 : 0) : "memory");
+  }
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // A fragments (16 rows x DK) of this warp's rows, one x4 per 16-wide k step.
 template <int DK>
@@ -119,10 +138,13 @@ struct KernelArgs {
 
 // ------------------------------------------------------------------------------------------------ forward
 template <int DK>
+struct FwdSmem { typename Smem<DK>::Tile q, k[2], v[2]; int mask[2][kTile]; };
+
+template <int DK>
 __global__ void __launch_bounds__(kWarps * 32)
 attn_fwd_kernel(const KernelArgs p) {
-  __shared__ __align__(16) typename Smem<DK>::Tile sQ, sK, sV;
-  __shared__ int sMask[kTile];
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  FwdSmem<DK>& sm = *reinterpret_cast<FwdSmem<DK>*>(smem_raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
   const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * kTile;
   const bf16* Q = p.q + size_t(b) * p.Sq * p.ldq;
@@ -130,36 +152,42 @@ attn_fwd_kernel(const KernelArgs p) {
   const bf16* V = p.v + size_t(b) * p.Sk * p.ldv;
   const long long* toks = p.key_tokens + size_t(b) * p.Sk;
 
-  load_tile<DK>(sQ, Q, p.ldq, q0, p.Sq, h * DK);
-  __syncthreads();
-  uint32_t qa[DK / 16][4];
-  load_a_frags<DK>(qa, sQ, warp * 16, lane);
+  // Future key tiles are exactly zero-weight under the causal mask unless a row is fully masked, which
+  // needs token[0] == PAD; only then must every tile be visited to reproduce the uniform row.
+  int kv_end = p.Sk;
+  if (p.causal && toks[0] != 0) kv_end = min(p.Sk, q0 + kTile);
+  const int ntiles = (kv_end + kTile - 1) / kTile;
 
+  auto issue_kv = [&](int it) {
+    const int buf = it & 1, k0 = it * kTile;
+    load_tile_async<DK>(sm.k[buf], K, p.ldk, k0, p.Sk, h * DK);
+    load_tile_async<DK>(sm.v[buf], V, p.ldv, k0, p.Sk, h * DK);
+    if (threadIdx.x < kTile) {
+      const int j = k0 + threadIdx.x;
+      sm.mask[buf][threadIdx.x] = (j >= p.Sk) ? 2 : (toks[j] == 0 ? 1 : 0);
+    }
+  };
+  load_tile_async<DK>(sm.q, Q, p.ldq, q0, p.Sq, h * DK);
+  issue_kv(0);
+  cp_async_commit();
+
+  uint32_t qa[DK / 16][4];
   float o[DK / 8][4];
 #pragma unroll
   for (int i = 0; i < DK / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
   float m[2] = {-INFINITY, -INFINITY}, l[2] = {0.f, 0.f};
   const int r0 = q0 + warp * 16 + g;  // this thread's rows: r0 and r0 + 8
 
-  // Future key tiles are exactly zero-weight under the causal mask unless a row is fully masked, which
-  // needs token[0] == PAD; only then must every tile be visited to reproduce the uniform row.
-  int kv_end = p.Sk;
-  if (p.causal && toks[0] != 0) kv_end = min(p.Sk, q0 + kTile);
-
-  for (int k0 = 0; k0 < kv_end; k0 += kTile) {
+  for (int it = 0; it < ntiles; ++it) {
+    const int buf = it & 1, k0 = it * kTile;
+    if (it + 1 < ntiles) { issue_kv(it + 1); cp_async_commit(); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
     __syncthreads();
-    load_tile<DK>(sK, K, p.ldk, k0, p.Sk, h * DK);
-    load_tile<DK>(sV, V, p.ldv, k0, p.Sk, h * DK);
-    if (threadIdx.x < kTile) {
-      const int j = k0 + threadIdx.x;
-      sMask[threadIdx.x] = (j >= p.Sk) ? 2 : (toks[j] == 0 ? 1 : 0);
-    }
-    __syncthreads();
+    if (it == 0) load_a_frags<DK>(qa, sm.q, warp * 16, lane);
 
     float s[kTile / 8][4];
 #pragma unroll
     for (int i = 0; i < kTile / 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
-    mma_a_tT<DK>(s, qa, sK, lane);
+    mma_a_tT<DK>(s, qa, sm.k[buf], lane);
 
     float mx[2] = {-INFINITY, -INFINITY};
 #pragma unroll
@@ -168,7 +196,7 @@ attn_fwd_kernel(const KernelArgs p) {
       for (int e = 0; e < 4; ++e) {
         const int jl = nb * 8 + t4 * 2 + (e & 1);
         const int row = r0 + (e >> 1) * 8;
-        const int mk = sMask[jl];
+        const int mk = sm.mask[buf][jl];
         float v = s[nb][e] * p.scale_log2;
         if (mk == 1 || (p.causal && k0 + jl > row)) v = kMasked;
         if (mk == 2) v = -INFINITY;
@@ -197,7 +225,8 @@ attn_fwd_kernel(const KernelArgs p) {
     for (int r = 0; r < 2; ++r) l[r] = l[r] * corr[r] + quad_sum(rs[r]);
 #pragma unroll
     for (int i = 0; i < DK / 8; ++i) { o[i][0] *= corr[0]; o[i][1] *= corr[0]; o[i][2] *= corr[1]; o[i][3] *= corr[1]; }
-    mma_p_t<DK>(o, s, sV, lane);
+    mma_p_t<DK>(o, s, sm.v[buf], lane);
+    __syncthreads();  // everyone is done with this buffer before the prefetch two tiles ahead overwrites it
   }
 
   const float inv[2] = {1.f / l[0], 1.f / l[1]};
@@ -220,10 +249,13 @@ attn_fwd_kernel(const KernelArgs p) {
 // ------------------------------------------------------------------------------------------------ backward: dQ (+ delta)
 // One CTA per 64-row Q tile; recomputes P per KV tile:  dS = P * (dO V^T - delta);  dQ = scale * dS K.
 template <int DK>
+struct DqSmem { typename Smem<DK>::Tile q, d_o, k[2], v[2]; int mask[2][kTile]; };
+
+template <int DK>
 __global__ void __launch_bounds__(kWarps * 32)
 attn_bwd_dq_kernel(const KernelArgs p) {
-  __shared__ __align__(16) typename Smem<DK>::Tile sQ, sK, sV;  // sQ is reused for dO
-  __shared__ int sMask[kTile];
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  DqSmem<DK>& sm = *reinterpret_cast<DqSmem<DK>*>(smem_raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
   const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * kTile;
   const bf16* K = p.k + size_t(b) * p.Sk * p.ldk;
@@ -231,7 +263,25 @@ attn_bwd_dq_kernel(const KernelArgs p) {
   const long long* toks = p.key_tokens + size_t(b) * p.Sk;
   const int r0 = q0 + warp * 16 + g;
 
-  // delta = rowsum(dO * O) for this thread's two rows (each row's DK columns are spread over the quad)
+  int kv_end = p.Sk;
+  if (p.causal && toks[0] != 0) kv_end = min(p.Sk, q0 + kTile);
+  const int ntiles = (kv_end + kTile - 1) / kTile;
+  auto issue_kv = [&](int it) {
+    const int buf = it & 1, k0 = it * kTile;
+    load_tile_async<DK>(sm.k[buf], K, p.ldk, k0, p.Sk, h * DK);
+    load_tile_async<DK>(sm.v[buf], V, p.ldv, k0, p.Sk, h * DK);
+    if (threadIdx.x < kTile) {
+      const int j = k0 + threadIdx.x;
+      sm.mask[buf][threadIdx.x] = (j >= p.Sk) ? 2 : (toks[j] == 0 ? 1 : 0);
+    }
+  };
+  load_tile_async<DK>(sm.q, p.q + size_t(b) * p.Sq * p.ldq, p.ldq, q0, p.Sq, h * DK);
+  load_tile_async<DK>(sm.d_o, p.d_o + size_t(b) * p.Sq * p.lddo, p.lddo, q0, p.Sq, h * DK);
+  issue_kv(0);
+  cp_async_commit();
+
+  // delta = rowsum(dO * O) for this thread's two rows (each row's DK columns are spread over the quad);
+  // these global loads are in flight together with the tile copies above.
   float delta[2] = {0.f, 0.f}, lse_m[2] = {0.f, 0.f}, lse_l[2] = {0.f, 0.f};
 #pragma unroll
   for (int r = 0; r < 2; ++r) {
@@ -240,9 +290,11 @@ attn_bwd_dq_kernel(const KernelArgs p) {
       const bf16* po = p.o + (size_t(b) * p.Sq + row) * p.ldo + h * DK;
       const bf16* pd = p.d_o + (size_t(b) * p.Sq + row) * p.lddo + h * DK;
       float acc = 0.f;
-      for (int c = t4 * 2; c < DK; c += 8) {
-        const uint32_t uo = *reinterpret_cast<const uint32_t*>(po + c), ud = *reinterpret_cast<const uint32_t*>(pd + c);
-        acc += ptx::bf16_lo(uo) * ptx::bf16_lo(ud) + ptx::bf16_hi(uo) * ptx::bf16_hi(ud);
+#pragma unroll
+      for (int c = t4 * 4; c < DK; c += 16) {
+        const uint2 uo = *reinterpret_cast<const uint2*>(po + c), ud = *reinterpret_cast<const uint2*>(pd + c);
+        acc += ptx::bf16_lo(uo.x) * ptx::bf16_lo(ud.x) + ptx::bf16_hi(uo.x) * ptx::bf16_hi(ud.x) +
+               ptx::bf16_lo(uo.y) * ptx::bf16_lo(ud.y) + ptx::bf16_hi(uo.y) * ptx::bf16_hi(ud.y);
       }
       delta[r] = acc;
       const float2 ml = reinterpret_cast<const float2*>(p.lse)[(size_t(b) * p.H + h) * p.Sq + row];
@@ -252,50 +304,36 @@ attn_bwd_dq_kernel(const KernelArgs p) {
     if (t4 == 0 && row < p.Sq) p.delta[(size_t(b) * p.H + h) * p.Sq + row] = delta[r];
   }
 
-  load_tile<DK>(sQ, p.q + size_t(b) * p.Sq * p.ldq, p.ldq, q0, p.Sq, h * DK);
-  __syncthreads();
-  uint32_t qa[DK / 16][4];
-  load_a_frags<DK>(qa, sQ, warp * 16, lane);
-  __syncthreads();
-  load_tile<DK>(sQ, p.d_o + size_t(b) * p.Sq * p.lddo, p.lddo, q0, p.Sq, h * DK);
-  __syncthreads();
-  uint32_t doa[DK / 16][4];
-  load_a_frags<DK>(doa, sQ, warp * 16, lane);
-
+  uint32_t qa[DK / 16][4], doa[DK / 16][4];
   float dq[DK / 8][4];
 #pragma unroll
   for (int i = 0; i < DK / 8; ++i) dq[i][0] = dq[i][1] = dq[i][2] = dq[i][3] = 0.f;
 
-  int kv_end = p.Sk;
-  if (p.causal && toks[0] != 0) kv_end = min(p.Sk, q0 + kTile);
-  for (int k0 = 0; k0 < kv_end; k0 += kTile) {
+  for (int it = 0; it < ntiles; ++it) {
+    const int buf = it & 1, k0 = it * kTile;
+    if (it + 1 < ntiles) { issue_kv(it + 1); cp_async_commit(); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
     __syncthreads();
-    load_tile<DK>(sK, K, p.ldk, k0, p.Sk, h * DK);
-    load_tile<DK>(sV, V, p.ldv, k0, p.Sk, h * DK);
-    if (threadIdx.x < kTile) {
-      const int j = k0 + threadIdx.x;
-      sMask[threadIdx.x] = (j >= p.Sk) ? 2 : (toks[j] == 0 ? 1 : 0);
-    }
-    __syncthreads();
+    if (it == 0) { load_a_frags<DK>(qa, sm.q, warp * 16, lane); load_a_frags<DK>(doa, sm.d_o, warp * 16, lane); }
     float s[kTile / 8][4], dp[kTile / 8][4];
 #pragma unroll
     for (int i = 0; i < kTile / 8; ++i) { s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f; dp[i][0] = dp[i][1] = dp[i][2] = dp[i][3] = 0.f; }
-    mma_a_tT<DK>(s, qa, sK, lane);
-    mma_a_tT<DK>(dp, doa, sV, lane);
+    mma_a_tT<DK>(s, qa, sm.k[buf], lane);
+    mma_a_tT<DK>(dp, doa, sm.v[buf], lane);
 #pragma unroll
     for (int nb = 0; nb < kTile / 8; ++nb) {
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         const int jl = nb * 8 + t4 * 2 + (e & 1);
         const int row = r0 + (e >> 1) * 8;
-        const int mk = sMask[jl];
+        const int mk = sm.mask[buf][jl];
         float v = s[nb][e] * p.scale_log2;
         if (mk == 1 || (p.causal && k0 + jl > row)) v = kMasked;
         const float pr = (mk == 2) ? 0.f : exp2f((v - lse_m[e >> 1]) - lse_l[e >> 1]);
         s[nb][e] = pr * (dp[nb][e] - delta[e >> 1]);  // dS
       }
     }
-    mma_p_t<DK>(dq, s, sK, lane);
+    mma_p_t<DK>(dq, s, sm.k[buf], lane);
+    __syncthreads();
   }
 #pragma unroll
   for (int r = 0; r < 2; ++r) {
@@ -313,10 +351,13 @@ attn_bwd_dq_kernel(const KernelArgs p) {
 // One CTA per 64-key tile (16 keys per warp), looping over Q tiles, in the transposed formulation:
 //   S^T = K Q^T;  P^T = exp2(S^T - lse[q]);  dV += P^T dO;  dP^T = V dO^T;  dS^T = P^T (dP^T - delta[q]);  dK += scale dS^T Q
 template <int DK>
+struct DkvSmem { typename Smem<DK>::Tile k, v, q[2], d_o[2]; float lse_m[2][kTile], lse_l[2][kTile], delta[2][kTile]; };
+
+template <int DK>
 __global__ void __launch_bounds__(kWarps * 32)
 attn_bwd_dkv_kernel(const KernelArgs p) {
-  __shared__ __align__(16) typename Smem<DK>::Tile sK, sQ, sDO;  // sK is reused for V while building fragments
-  __shared__ float sLseM[kTile], sLseL[kTile], sDelta[kTile];
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  DkvSmem<DK>& sm = *reinterpret_cast<DkvSmem<DK>*>(smem_raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
   const int b = blockIdx.z, h = blockIdx.y, k0 = blockIdx.x * kTile;
   const bf16* Q = p.q + size_t(b) * p.Sq * p.ldq;
@@ -327,38 +368,40 @@ attn_bwd_dkv_kernel(const KernelArgs p) {
 #pragma unroll
   for (int r = 0; r < 2; ++r) { const int j = key0 + r * 8; kmask[r] = (j >= p.Sk) ? 2 : (toks[j] == 0 ? 1 : 0); }
 
-  load_tile<DK>(sK, p.k + size_t(b) * p.Sk * p.ldk, p.ldk, k0, p.Sk, h * DK);
-  __syncthreads();
-  uint32_t ka[DK / 16][4];
-  load_a_frags<DK>(ka, sK, warp * 16, lane);
-  __syncthreads();
-  load_tile<DK>(sK, p.v + size_t(b) * p.Sk * p.ldv, p.ldv, k0, p.Sk, h * DK);
-  __syncthreads();
-  uint32_t va[DK / 16][4];
-  load_a_frags<DK>(va, sK, warp * 16, lane);
+  int q_begin = 0;
+  if (p.causal && toks[0] != 0) q_begin = k0;  // earlier query tiles never see these keys
+  const int ntiles = (p.Sq - q_begin + kTile - 1) / kTile;
+  auto issue_q = [&](int it) {
+    const int buf = it & 1, q0 = q_begin + it * kTile;
+    load_tile_async<DK>(sm.q[buf], Q, p.ldq, q0, p.Sq, h * DK);
+    load_tile_async<DK>(sm.d_o[buf], DO, p.lddo, q0, p.Sq, h * DK);
+    if (threadIdx.x < kTile) {
+      const int i = q0 + threadIdx.x;
+      const float2 ml = (i < p.Sq) ? reinterpret_cast<const float2*>(p.lse)[(size_t(b) * p.H + h) * p.Sq + i] : make_float2(INFINITY, 0.f);
+      sm.lse_m[buf][threadIdx.x] = ml.x; sm.lse_l[buf][threadIdx.x] = ml.y;  // exp2(x - inf) = 0 for rows past Sq
+      sm.delta[buf][threadIdx.x] = (i < p.Sq) ? p.delta[(size_t(b) * p.H + h) * p.Sq + i] : 0.f;
+    }
+  };
+  load_tile_async<DK>(sm.k, p.k + size_t(b) * p.Sk * p.ldk, p.ldk, k0, p.Sk, h * DK);
+  load_tile_async<DK>(sm.v, p.v + size_t(b) * p.Sk * p.ldv, p.ldv, k0, p.Sk, h * DK);
+  if (ntiles > 0) issue_q(0);
+  cp_async_commit();
 
+  uint32_t ka[DK / 16][4], va[DK / 16][4];
   float dk[DK / 8][4], dv[DK / 8][4];
 #pragma unroll
   for (int i = 0; i < DK / 8; ++i) { dk[i][0] = dk[i][1] = dk[i][2] = dk[i][3] = 0.f; dv[i][0] = dv[i][1] = dv[i][2] = dv[i][3] = 0.f; }
 
-  int q_begin = 0;
-  if (p.causal && toks[0] != 0) q_begin = (k0 / kTile) * kTile;  // earlier query tiles never see these keys
-  for (int q0 = q_begin; q0 < p.Sq; q0 += kTile) {
+  for (int it = 0; it < ntiles; ++it) {
+    const int buf = it & 1, q0 = q_begin + it * kTile;
+    if (it + 1 < ntiles) { issue_q(it + 1); cp_async_commit(); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
     __syncthreads();
-    load_tile<DK>(sQ, Q, p.ldq, q0, p.Sq, h * DK);
-    load_tile<DK>(sDO, DO, p.lddo, q0, p.Sq, h * DK);
-    if (threadIdx.x < kTile) {
-      const int i = q0 + threadIdx.x;
-      const float2 ml = (i < p.Sq) ? reinterpret_cast<const float2*>(p.lse)[(size_t(b) * p.H + h) * p.Sq + i] : make_float2(INFINITY, 0.f);
-      sLseM[threadIdx.x] = ml.x; sLseL[threadIdx.x] = ml.y;  // exp2(x - inf) = 0 for rows past Sq
-      sDelta[threadIdx.x] = (i < p.Sq) ? p.delta[(size_t(b) * p.H + h) * p.Sq + i] : 0.f;
-    }
-    __syncthreads();
+    if (it == 0) { load_a_frags<DK>(ka, sm.k, warp * 16, lane); load_a_frags<DK>(va, sm.v, warp * 16, lane); }
     float st[kTile / 8][4], dpt[kTile / 8][4];
 #pragma unroll
     for (int i = 0; i < kTile / 8; ++i) { st[i][0] = st[i][1] = st[i][2] = st[i][3] = 0.f; dpt[i][0] = dpt[i][1] = dpt[i][2] = dpt[i][3] = 0.f; }
-    mma_a_tT<DK>(st, ka, sQ, lane);
-    mma_a_tT<DK>(dpt, va, sDO, lane);
+    mma_a_tT<DK>(st, ka, sm.q[buf], lane);
+    mma_a_tT<DK>(dpt, va, sm.d_o[buf], lane);
     float pt[kTile / 8][4];
 #pragma unroll
     for (int nb = 0; nb < kTile / 8; ++nb) {
@@ -369,13 +412,14 @@ attn_bwd_dkv_kernel(const KernelArgs p) {
         const int mk = kmask[e >> 1];
         float v = st[nb][e] * p.scale_log2;
         if (mk == 1 || (p.causal && key > q0 + il)) v = kMasked;
-        const float pr = (mk == 2) ? 0.f : exp2f((v - sLseM[il]) - sLseL[il]);
+        const float pr = (mk == 2) ? 0.f : exp2f((v - sm.lse_m[buf][il]) - sm.lse_l[buf][il]);
         pt[nb][e] = pr;
-        st[nb][e] = pr * (dpt[nb][e] - sDelta[il]);   // dS^T
+        st[nb][e] = pr * (dpt[nb][e] - sm.delta[buf][il]);   // dS^T
       }
     }
-    mma_p_t<DK>(dv, pt, sDO, lane);
-    mma_p_t<DK>(dk, st, sQ, lane);
+    mma_p_t<DK>(dv, pt, sm.d_o[buf], lane);
+    mma_p_t<DK>(dk, st, sm.q[buf], lane);
+    __syncthreads();
   }
 #pragma unroll
   for (int r = 0; r < 2; ++r) {
@@ -414,6 +458,24 @@ KernelArgs pack(const AttnArgs& a) {
   return p;
 }
 
+template <typename Kern>
+int launch_attn(Kern kern, size_t smem, dim3 grid, const KernelArgs& p, cudaStream_t stream) {
+  if (smem > 48 * 1024) {
+    static std::mutex mu;
+    static std::set<const void*> configured;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!configured.count(reinterpret_cast<const void*>(kern))) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+      if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(attention): %s", cudaGetErrorString(e));
+      configured.insert(reinterpret_cast<const void*>(kern));
+    }
+  }
+  kern<<<grid, kWarps * 32, smem, stream>>>(p);
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
 }  // namespace
 
 int attention_fwd(const AttnArgs& a, cudaStream_t stream) {
@@ -421,13 +483,10 @@ int attention_fwd(const AttnArgs& a, cudaStream_t stream) {
   const KernelArgs p = pack(a);
   const dim3 grid((a.Sq + kTile - 1) / kTile, a.H, a.B);
   switch (a.dk) {
-    case 16: attn_fwd_kernel<16><<<grid, kWarps * 32, 0, stream>>>(p); break;
-    case 32: attn_fwd_kernel<32><<<grid, kWarps * 32, 0, stream>>>(p); break;
-    default: attn_fwd_kernel<64><<<grid, kWarps * 32, 0, stream>>>(p); break;
+    case 16: return launch_attn(attn_fwd_kernel<16>, sizeof(FwdSmem<16>), grid, p, stream);
+    case 32: return launch_attn(attn_fwd_kernel<32>, sizeof(FwdSmem<32>), grid, p, stream);
+    default: return launch_attn(attn_fwd_kernel<64>, sizeof(FwdSmem<64>), grid, p, stream);
   }
-  B200XF_CUDA(cudaGetLastError());
-  count_launch();
-  return 0;
 }
 
 int attention_bwd(const AttnArgs& a, cudaStream_t stream) {
@@ -435,13 +494,16 @@ int attention_bwd(const AttnArgs& a, cudaStream_t stream) {
   const KernelArgs p = pack(a);
   const dim3 gq((a.Sq + kTile - 1) / kTile, a.H, a.B), gk((a.Sk + kTile - 1) / kTile, a.H, a.B);
   switch (a.dk) {
-    case 16: attn_bwd_dq_kernel<16><<<gq, kWarps * 32, 0, stream>>>(p); attn_bwd_dkv_kernel<16><<<gk, kWarps * 32, 0, stream>>>(p); break;
-    case 32: attn_bwd_dq_kernel<32><<<gq, kWarps * 32, 0, stream>>>(p); attn_bwd_dkv_kernel<32><<<gk, kWarps * 32, 0, stream>>>(p); break;
-    default: attn_bwd_dq_kernel<64><<<gq, kWarps * 32, 0, stream>>>(p); attn_bwd_dkv_kernel<64><<<gk, kWarps * 32, 0, stream>>>(p); break;
+    case 16:
+      B200XF_TRY(launch_attn(attn_bwd_dq_kernel<16>, sizeof(DqSmem<16>), gq, p, stream));
+      return launch_attn(attn_bwd_dkv_kernel<16>, sizeof(DkvSmem<16>), gk, p, stream);
+    case 32:
+      B200XF_TRY(launch_attn(attn_bwd_dq_kernel<32>, sizeof(DqSmem<32>), gq, p, stream));
+      return launch_attn(attn_bwd_dkv_kernel<32>, sizeof(DkvSmem<32>), gk, p, stream);
+    default:
+      B200XF_TRY(launch_attn(attn_bwd_dq_kernel<64>, sizeof(DqSmem<64>), gq, p, stream));
+      return launch_attn(attn_bwd_dkv_kernel<64>, sizeof(DkvSmem<64>), gk, p, stream);
   }
-  B200XF_CUDA(cudaGetLastError());
-  count_launch(2);
-  return 0;
 }
 
 }  // namespace b200xf
