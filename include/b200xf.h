@@ -115,6 +115,11 @@ int b200xf_gemm_bf16(const void* a, int lda, int a_mn, const void* b, int ldb, i
                      int accumulate, int M, int N, int K, const float* bias, int relu, const void* resid, int ldr,
                      int resid_op, float alpha, int force_bn, int split_k, void* stream);
 
+/* Debug aid (no counterpart in the reference): when given a DEVICE buffer of 8 * 148 uint64, every later GEMM launch
+ * records %globaltimer stamps per CTA (start, set-up done, first operands landed, last MMA issued, accumulator ready,
+ * epilogue done, exit).  Pass NULL to switch it off. */
+int b200xf_debug_gemm_trace(void* device_u64_buffer);
+
 /* scaled_dot_product_attention + masks + split/merge heads (transformer_model.py:56-70,73-109,124-131,160-163).
  * q [B*Sq, ldq], k/v [B*Sk, ld*], o [B*Sq, ldo] bf16, head h in columns [h*dk,(h+1)*dk); key_tokens [B,Sk] int64;
  * lse fp32 [B,H,Sq,2] = {row max, log2(row sum)} of the scaled, masked scores in the log2 domain. */

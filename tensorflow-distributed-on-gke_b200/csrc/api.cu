@@ -101,6 +101,11 @@ int b200xf_gemm_bf16(const void* a, int lda, int a_mn, const void* b, int ldb, i
   return gemm_bf16(g, static_cast<cudaStream_t>(stream));
 }
 
+int b200xf_debug_gemm_trace(void* device_u64_buffer) {
+  gemm_set_trace(static_cast<unsigned long long*>(device_u64_buffer));
+  return 0;
+}
+
 int b200xf_attention_fwd(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, void* o, int ldo, float* lse,
                          const int64_t* key_tokens, int causal, int B, int H, int Sq, int Sk, int dk, void* stream) {
   AttnArgs a;

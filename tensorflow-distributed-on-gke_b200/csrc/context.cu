@@ -318,6 +318,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
     B200XF_CUDA(cudaMemcpyAsync(pe_tgt, pe.data(), size_t(hp.maximum_target_length) * d * 4, cudaMemcpyHostToDevice, stream));
     B200XF_CUDA(cudaStreamSynchronize(stream));
   }
+  if (const char* e = getenv("B200XF_OVERLAP_UPDATE")) overlap_single = atoi(e) != 0;
   adam.beta1 = hp.adam_beta_1; adam.beta2 = hp.adam_beta_2; adam.eps = hp.adam_epsilon;
   adam.rsqrt_d_model = 1.0f / sqrtf(float(d));
   adam.warmup_pow_m15 = float(pow(double(hp.warmup_steps), -1.5));
@@ -630,20 +631,20 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
   return 0;
 }
 
-// Called each time backward finishes one layout section.  With a communicator attached and updates enabled,
-// completed sections are grouped into buckets of >= bucket_bytes; each bucket is all-reduced on the comm
-// stream (after an event on the compute stream) and its Adam update is chained behind the reduce, so both
-// hide under the remaining backward.  Without a communicator nothing happens here (one Adam at the end).
+// Called each time backward finishes one layout section.  In a train step, completed sections are grouped into
+// buckets of >= bucket_bytes; each bucket is all-reduced (when a communicator is attached) on the side stream, after
+// an event on the compute stream, and its Adam update is chained behind the reduce, so both hide under the rest of
+// the backward pass (whose small kernels leave HBM bandwidth idle).
 int Context::section_done() {
   const size_t idx = next_section++;
-  if (!overlap_update || !comm) return 0;
+  if (!overlap_update) return 0;
   const size_t end = sections[idx].second;
   const bool last = (idx + 1 == sections.size());
   if (!last && (end - bucket_begin) * sizeof(float) < bucket_bytes) return 0;
   B200XF_TRY(flush_reductions());
   B200XF_CUDA(cudaEventRecord(ev_ready, stream));
   B200XF_CUDA(cudaStreamWaitEvent(comm_stream, ev_ready, 0));
-  B200XF_TRY(allreduce(grads + bucket_begin, end - bucket_begin, comm_stream));
+  if (comm) B200XF_TRY(allreduce(grads + bucket_begin, end - bucket_begin, comm_stream));
   B200XF_TRY(adam_step(params + bucket_begin, grads + bucket_begin, adam_m + bucket_begin, adam_v + bucket_begin,
                        shadow + bucket_begin, end - bucket_begin, iterations_dev, adam, 1, comm_stream));
   bucket_begin = end;
@@ -671,25 +672,25 @@ int Context::step_device(const long long* inp, const long long* target, int B, i
   B200XF_TRY(forward(inp, tok_tgt_in, B, S, T, nullptr));
   B200XF_TRY(loss_and_grad(B * T, workers_count, mode != 0));
   if (mode >= 1) {
-    overlap_update = (mode == 2) && comm != nullptr;
+    overlap_update = (mode == 2) && (comm != nullptr || overlap_single);
     bucket_begin = 0;
     B200XF_TRY(backward(inp, tok_tgt_in, B, S, T));
   }
   if (mode == 2) {
+    // metrics: local values stay in metrics[0..2]; the cross-replica sums go to metrics[3..5]
+    B200XF_CUDA(cudaMemcpyAsync(metrics + 3, metrics, 3 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
     if (comm) {
-      // metrics: local values stay in metrics[0..2]; reduced copy in metrics[3..5]
-      B200XF_CUDA(cudaMemcpyAsync(metrics + 3, metrics, 3 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
       B200XF_CUDA(cudaEventRecord(ev_ready, stream));
       B200XF_CUDA(cudaStreamWaitEvent(comm_stream, ev_ready, 0));
       B200XF_TRY(allreduce(metrics + 3, 3, comm_stream));
-      B200XF_CUDA(cudaEventRecord(ev_done, comm_stream));
-      B200XF_CUDA(cudaStreamWaitEvent(stream, ev_done, 0));  // weights + metrics ready for whatever follows
-      grads_clean = true;
-    } else {
-      B200XF_CUDA(cudaMemcpyAsync(metrics + 3, metrics, 3 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
-      B200XF_TRY(adam_step(params, grads, adam_m, adam_v, shadow, total_params, iterations_dev, adam, 1, stream));
-      grads_clean = true;
     }
+    if (overlap_update) {
+      B200XF_CUDA(cudaEventRecord(ev_done, comm_stream));
+      B200XF_CUDA(cudaStreamWaitEvent(stream, ev_done, 0));  // every bucket's update (and the metrics) done before what follows
+    } else {
+      B200XF_TRY(adam_step(params, grads, adam_m, adam_v, shadow, total_params, iterations_dev, adam, 1, stream));
+    }
+    grads_clean = true;
     B200XF_TRY(increment_counter(iterations_dev, stream));
   } else {
     B200XF_CUDA(cudaMemcpyAsync(metrics + 3, metrics, 3 * sizeof(float), cudaMemcpyDeviceToDevice, stream));

@@ -63,6 +63,7 @@ struct Context {
   cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
   size_t bucket_bytes = size_t(32) << 20, bucket_begin = 0, next_section = 0;
   bool overlap_update = false;
+  bool overlap_single = false;  // single GPU: run each bucket's Adam on the side stream under the rest of backward (B200XF_OVERLAP_UPDATE=1)
 
   ~Context();
   int init(const b200xf_hparams& h, int dev, cudaStream_t s);

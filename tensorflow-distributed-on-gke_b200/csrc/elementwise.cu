@@ -111,9 +111,27 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
 #pragma unroll
     for (int j = 0; j < 8; ++j) { acc_g[c][j] = acc_b[c][j] = acc_c[c][j] = 0.f; gam[c][j] = (col < d) ? __ldg(gamma + col + j) : 0.f; }
   }
-  for (int row = blockIdx.x * kLnWarps + warp; row < rows; row += gridDim.x * kLnWarps) {
+  // software pipeline: the next row's loads are issued before the current row's reductions
+  uint4 nxt_dy[CH], nxt_z[CH];
+  float nxt_mean = 0.f, nxt_rstd = 0.f;
+  auto fetch = [&](int row) {
     const size_t base = size_t(row) * d;
-    const float mean = mean_in[row], rstd = rstd_in[row];
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+      const int col = (c * 32 + lane) * 8;
+      if (col < d) { nxt_dy[c] = *reinterpret_cast<const uint4*>(dy + base + col); nxt_z[c] = *reinterpret_cast<const uint4*>(z + base + col); }
+    }
+    nxt_mean = mean_in[row]; nxt_rstd = rstd_in[row];
+  };
+  const int row_first = blockIdx.x * kLnWarps + warp, row_step = gridDim.x * kLnWarps;
+  if (row_first < rows) fetch(row_first);
+  for (int row = row_first; row < rows; row += row_step) {
+    const size_t base = size_t(row) * d;
+    const float mean = nxt_mean, rstd = nxt_rstd;
+    uint4 cur_dy[CH], cur_z[CH];
+#pragma unroll
+    for (int c = 0; c < CH; ++c) { cur_dy[c] = nxt_dy[c]; cur_z[c] = nxt_z[c]; }
+    if (row + row_step < rows) fetch(row + row_step);
     float xh[CH][8], g[CH][8];
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
@@ -121,8 +139,8 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
       const int col = (c * 32 + lane) * 8;
       if (col < d) {
         float a[8], b[8];
-        unpack8(*reinterpret_cast<const uint4*>(dy + base + col), a);
-        unpack8(*reinterpret_cast<const uint4*>(z + base + col), b);
+        unpack8(cur_dy[c], a);
+        unpack8(cur_z[c], b);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           xh[c][j] = (b[j] - mean) * rstd;
@@ -212,7 +230,7 @@ int layernorm_fwd(const bf16* x, const bf16* resid, const float* gamma, const fl
   return 0;
 }
 
-int ln_bwd_parts(int rows) { return std::max(1, std::min((rows + kLnWarps - 1) / kLnWarps, num_sms())); }
+int ln_bwd_parts(int rows) { return std::max(1, std::min((rows + kLnWarps - 1) / kLnWarps, 2 * num_sms())); }
 size_t ln_bwd_scratch_floats(int rows, int d) { return size_t(ln_bwd_parts(rows)) * 3 * d; }
 
 int layernorm_bwd_partial(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const float* gamma, bf16* dz, int rows,

@@ -39,26 +39,80 @@ struct Cfg {
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kSmem = kStages * kStageBytes + 4 * 2 * 4096 /*store staging*/ + 1024 /*align slack*/ + 256 /*barriers*/;
   static constexpr int kTmemCols = 2 * BN;  // double-buffered accumulator
 };
 
 struct GemmParams {
   int M, N, K;
   int tiles_m, tiles_n, splits, kb_per_split;
-  void* d; int ldd; int d_fp32; int accumulate; int d_vec;  // d_vec: rows are 16-byte aligned -> vector stores
+  void* d; int ldd; int d_fp32; int accumulate; int d_vec; int d_tma;  // d_vec: rows are 16-byte aligned -> vector stores
   const float* bias; int relu;
   const __nv_bfloat16* resid; int ldr; int resid_op;  // 0 none, 1 add, 2 relu-mask
   float alpha;
+  unsigned long long* trace;  // debug: 8 globaltimer stamps per CTA (null in production)
 };
+
+// bias add, ReLU, residual add / ReLU mask on 32 accumulator columns [col0, col0+32) of one output row.
+__device__ __forceinline__ void epilogue_math(float* f, const GemmParams& p, int row, bool row_ok, int col0, bool add_bias) {
+  const bool full = col0 + 32 <= p.N;
+  if (add_bias) {
+    if (full) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+        f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) if (col0 + j < p.N) f[j] += __ldg(p.bias + col0 + j);
+    }
+  }
+  if (p.relu) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+  }
+  if (p.resid_op && row_ok) {
+    const __nv_bfloat16* rp = p.resid + size_t(row) * p.ldr + col0;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      float r[8];
+      if (col0 + g * 8 + 8 <= p.N) {
+        const uint4 u = *reinterpret_cast<const uint4*>(rp + g * 8);
+        r[0] = ptx::bf16_lo(u.x); r[1] = ptx::bf16_hi(u.x); r[2] = ptx::bf16_lo(u.y); r[3] = ptx::bf16_hi(u.y);
+        r[4] = ptx::bf16_lo(u.z); r[5] = ptx::bf16_hi(u.z); r[6] = ptx::bf16_lo(u.w); r[7] = ptx::bf16_hi(u.w);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = (col0 + g * 8 + j < p.N) ? __bfloat162float(rp[g * 8 + j]) : 0.f;
+      }
+      if (p.resid_op == 1) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[g * 8 + j] += r[j];
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[g * 8 + j] = r[j] > 0.f ? f[g * 8 + j] : 0.f;
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ void stamp(const GemmParams& p, int slot) {
+  if (p.trace) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.trace[size_t(blockIdx.x) * 8 + slot] = t;
+  }
+}
 
 template <int BN, int A_MN, int B_MN>
 __global__ void __launch_bounds__(kThreads, 1)
-gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
+gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+            const __grid_constant__ CUtensorMap tmap_d, const GemmParams p) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint8_t* stage_base = smem + C::kStages * C::kStageBytes;  // 4 epilogue warps x 2 x 4 KB store staging
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_base + 4 * 2 * 4096);
   uint64_t* empty_bar = full_bar + C::kStages;
   uint64_t* tmem_full = empty_bar + C::kStages;
   uint64_t* tmem_empty = tmem_full + 2;
@@ -66,10 +120,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) stamp(p, 0);
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmap_a);
     ptx::prefetch_tmap(&tmap_b);
+    if (p.d_tma) ptx::prefetch_tmap(&tmap_d);
     for (int i = 0; i < C::kStages; ++i) { ptx::mbar_init(&full_bar[i], 1); ptx::mbar_init(&empty_bar[i], 1); }
     for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tmem_full[i], 1); ptx::mbar_init(&tmem_empty[i], 4); }
     ptx::fence_barrier_init();
@@ -82,6 +138,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) stamp(p, 1);
 
   const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
   const int total_kb = (p.K + BK - 1) / BK;
@@ -134,6 +191,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(&full_bar[s], ph);
           ptx::tc_fence_after();
+          if (it == 0 && kb == kb0) stamp(p, 2);
           const uint32_t sa = ptx::smem_u32(smem + s * C::kStageBytes);
           const uint32_t sb = sa + C::kABytes;
 #pragma unroll
@@ -146,6 +204,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           if (++s == C::kStages) { s = 0; ph ^= 1; }
         }
         ptx::umma_commit(&tmem_full[as]);  // accumulator complete -> epilogue
+        if (it == 0) stamp(p, 3);
       }
     }
   } else {
@@ -157,10 +216,59 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
       ptx::mbar_wait(&tmem_full[as], aph);
       ptx::tc_fence_after();
+      if (it == 0 && warp == 2 && lane == 0) stamp(p, 4);
       const int row = tm * BM + quarter * 32 + lane;
       const bool row_ok = row < p.M;
       const uint32_t taddr = tmem_base + as * BN + (uint32_t(quarter * 32) << 16);
       const bool add_bias = p.bias != nullptr && z == 0;
+      if (p.d_tma) {
+        // TMEM -> registers -> 128B-swizzled staging tile (32 rows x 128 B per warp, double buffered) -> TMA store /
+        // TMA reduce-add: coalesced, asynchronous, clipped to the tensor bounds by the hardware.
+        constexpr int kColsPerBox = 32;  // fp32: 32 columns = 128 B per row; bf16 packs two 32-column chunks per box
+        const int chunks = p.d_fp32 ? 1 : 2;
+        uint8_t* my_stage = stage_base + (warp - 2) * 2 * 4096;
+        int sidx = 0;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN / 32; c0 += chunks) {
+          const int colbase = tn * BN + c0 * 32;
+          if (colbase >= p.N) break;  // warp-uniform
+          uint8_t* buf = my_stage + sidx * 4096;
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");  // the store 2 boxes ago has read this buffer
+          __syncwarp();
+          for (int cc = 0; cc < chunks; ++cc) {
+            const int col0 = colbase + cc * 32;
+            uint32_t v[32];
+            ptx::tmem_ld_32x32(taddr + (c0 + cc) * 32, v);
+            ptx::tmem_ld_wait();
+            float f[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
+            if (col0 < p.N) epilogue_math(f, p, row, row_ok, col0, add_bias);
+            if (p.d_fp32) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q)  // 8 x 16-byte chunks per 128-byte row, XOR-swizzled by the row index
+                *reinterpret_cast<float4*>(buf + lane * 128 + ((q ^ (lane & 7)) << 4)) = make_float4(f[q * 4], f[q * 4 + 1], f[q * 4 + 2], f[q * 4 + 3]);
+            } else {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                uint4 u;
+                u.x = ptx::pack_bf16x2(f[q * 8], f[q * 8 + 1]); u.y = ptx::pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3]);
+                u.z = ptx::pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5]); u.w = ptx::pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]);
+                *reinterpret_cast<uint4*>(buf + lane * 128 + (((cc * 4 + q) ^ (lane & 7)) << 4)) = u;
+              }
+            }
+          }
+          ptx::fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            const int r0 = tm * BM + quarter * 32;
+            if (p.accumulate) ptx::tma_reduce_add_2d(&tmap_d, buf, colbase, r0); else ptx::tma_store_2d(&tmap_d, buf, colbase, r0);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+          sidx ^= 1;
+        }
+        (void)kColsPerBox;
+      } else {
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         const int col0 = tn * BN + c * 32;
@@ -171,45 +279,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
-        const bool full = col0 + 32 <= p.N;
-        if (add_bias) {
-          if (full) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
-              f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) if (col0 + j < p.N) f[j] += __ldg(p.bias + col0 + j);
-          }
-        }
-        if (p.relu) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-        }
-        if (p.resid_op && row_ok) {
-          const __nv_bfloat16* rp = p.resid + size_t(row) * p.ldr + col0;
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float r[8];
-            if (col0 + g * 8 + 8 <= p.N) {
-              const uint4 u = *reinterpret_cast<const uint4*>(rp + g * 8);
-              r[0] = ptx::bf16_lo(u.x); r[1] = ptx::bf16_hi(u.x); r[2] = ptx::bf16_lo(u.y); r[3] = ptx::bf16_hi(u.y);
-              r[4] = ptx::bf16_lo(u.z); r[5] = ptx::bf16_hi(u.z); r[6] = ptx::bf16_lo(u.w); r[7] = ptx::bf16_hi(u.w);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) r[j] = (col0 + g * 8 + j < p.N) ? __bfloat162float(rp[g * 8 + j]) : 0.f;
-            }
-            if (p.resid_op == 1) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) f[g * 8 + j] += r[j];
-            } else {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) f[g * 8 + j] = r[j] > 0.f ? f[g * 8 + j] : 0.f;
-            }
-          }
-        }
+        epilogue_math(f, p, row, row_ok, col0, add_bias);
         if (row_ok) {
           if (p.d_fp32) {
             float* dp = reinterpret_cast<float*>(p.d) + size_t(row) * p.ldd + col0;
@@ -244,10 +314,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           }
         }
       }
+      }
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tmem_empty[as]);
+      if (it == 0 && warp == 2 && lane == 0) stamp(p, 5);
     }
+    if (p.d_tma && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // staging smem must outlive the stores
   }
 
   ptx::tc_fence_before();
@@ -256,6 +329,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, C::kTmemCols);
   }
+  if (threadIdx.x == 0) stamp(p, 6);
 }
 
 // ------------------------------------------------------------------------ host side
@@ -276,28 +350,30 @@ EncodeTiledFn get_encode() {
 }
 
 struct MapKey {
-  const void* ptr; uint64_t inner, outer, ld; uint32_t box_outer;
+  const void* ptr; uint64_t inner, outer, ld; uint32_t box_outer; int kind;  // kind 0: bf16 operand/output (box 64 wide), 1: fp32 output (box 32 wide)
   bool operator<(const MapKey& o) const {
-    return std::tie(ptr, inner, outer, ld, box_outer) < std::tie(o.ptr, o.inner, o.outer, o.ld, o.box_outer);
+    return std::tie(ptr, inner, outer, ld, box_outer, kind) < std::tie(o.ptr, o.inner, o.outer, o.ld, o.box_outer, o.kind);
   }
 };
+unsigned long long* g_gemm_trace = nullptr;
 std::map<MapKey, CUtensorMap> g_map_cache;
 std::mutex g_map_mutex;
 
 // 2-D bf16 tensor map: inner (contiguous) extent, outer extent, row pitch ld (elements); box = 64 x box_outer, 128B swizzle.
-int get_tmap(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_outer, CUtensorMap* out) {
-  MapKey key{ptr, inner, outer, ld, box_outer};
+int get_tmap(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_outer, CUtensorMap* out, int kind = 0) {
+  MapKey key{ptr, inner, outer, ld, box_outer, kind};
   std::lock_guard<std::mutex> lock(g_map_mutex);
   auto it = g_map_cache.find(key);
   if (it != g_map_cache.end()) { *out = it->second; return 0; }
   EncodeTiledFn enc = get_encode();
   if (!enc) return set_error("cuTensorMapEncodeTiled entry point unavailable");
-  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (ld % 8)) return set_error("gemm operand must be 16-byte aligned with ld % 8 == 0");
+  const uint64_t elt = kind == 1 ? 4 : 2;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((ld * elt) % 16)) return set_error("gemm operand must be 16-byte aligned with a 16-byte multiple row pitch");
   cuuint64_t dims[2] = {inner, outer};
-  cuuint64_t strides[1] = {ld * 2};
-  cuuint32_t box[2] = {64, box_outer};
+  cuuint64_t strides[1] = {ld * elt};
+  cuuint32_t box[2] = {kind == 1 ? 32u : 64u, box_outer};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+  CUresult r = enc(out, kind == 1 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return set_error("cuTensorMapEncodeTiled failed (%d) inner=%llu outer=%llu ld=%llu", int(r),
@@ -308,7 +384,7 @@ int get_tmap(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint3
 }
 
 template <int BN, int A_MN, int B_MN>
-int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t stream) {
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const GemmParams& p, int grid, cudaStream_t stream) {
   auto kern = gemm_kernel<BN, A_MN, B_MN>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -316,7 +392,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, in
     if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gemm): %s", cudaGetErrorString(e));
     attr_set = true;
   }
-  kern<<<grid, kThreads, Cfg<BN>::kSmem, stream>>>(ta, tb, p);
+  kern<<<grid, kThreads, Cfg<BN>::kSmem, stream>>>(ta, tb, td, p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return set_error("gemm launch: %s", cudaGetErrorString(e));
   count_launch();
@@ -324,11 +400,11 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, in
 }
 
 template <int BN>
-int launch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t s) {
-  if (!a_mn && b_mn) return launch<BN, 0, 1>(ta, tb, p, grid, s);
-  if (!a_mn && !b_mn) return launch<BN, 0, 0>(ta, tb, p, grid, s);
-  if (a_mn && b_mn) return launch<BN, 1, 1>(ta, tb, p, grid, s);
-  return launch<BN, 1, 0>(ta, tb, p, grid, s);
+int launch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const GemmParams& p, int grid, cudaStream_t s) {
+  if (!a_mn && b_mn) return launch<BN, 0, 1>(ta, tb, td, p, grid, s);
+  if (!a_mn && !b_mn) return launch<BN, 0, 0>(ta, tb, td, p, grid, s);
+  if (a_mn && b_mn) return launch<BN, 1, 1>(ta, tb, td, p, grid, s);
+  return launch<BN, 1, 0>(ta, tb, td, p, grid, s);
 }
 
 }  // namespace
@@ -380,6 +456,7 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   p.bias = a.bias; p.relu = a.relu;
   p.resid = reinterpret_cast<const __nv_bfloat16*>(a.resid); p.ldr = a.ldr; p.resid_op = a.resid ? a.resid_op : 0;
   p.alpha = a.alpha;
+  p.trace = g_gemm_trace;
 
   CUtensorMap ta, tb;
   int rc;
@@ -390,14 +467,21 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   else rc = get_tmap(a.b, a.K, a.N, a.ldb, bn, &tb);
   if (rc) return rc;
 
+  // output through TMA (store / reduce-add) whenever its rows are 16-byte aligned with a 16-byte multiple pitch
+  CUtensorMap td = ta;
+  p.d_tma = ((reinterpret_cast<uintptr_t>(a.d) & 15) == 0) && ((size_t(a.ldd) * (a.d_fp32 ? 4 : 2)) % 16 == 0) && !a.no_tma_store;
+  if (p.d_tma) { rc = get_tmap(a.d, a.N, a.M, a.ldd, 32, &td, a.d_fp32 ? 1 : 0); if (rc) return rc; }
+
   const int total = tiles_m * tiles_n * splits;
   const int grid = min(total, nsm);
   switch (bn) {
-    case 64: return launch_major<64>(a.a_mn, a.b_mn, ta, tb, p, grid, stream);
-    case 128: return launch_major<128>(a.a_mn, a.b_mn, ta, tb, p, grid, stream);
-    default: return launch_major<256>(a.a_mn, a.b_mn, ta, tb, p, grid, stream);
+    case 64: return launch_major<64>(a.a_mn, a.b_mn, ta, tb, td, p, grid, stream);
+    case 128: return launch_major<128>(a.a_mn, a.b_mn, ta, tb, td, p, grid, stream);
+    default: return launch_major<256>(a.a_mn, a.b_mn, ta, tb, td, p, grid, stream);
   }
 }
+
+void gemm_set_trace(unsigned long long* dev_ptr) { g_gemm_trace = dev_ptr; }
 
 void gemm_clear_tensor_map_cache() {
   std::lock_guard<std::mutex> lock(g_map_mutex);

@@ -41,9 +41,11 @@ struct GemmArgs {
   const void* resid = nullptr; int ldr = 0; int resid_op = 0;  // 1 add, 2 relu-mask
   float alpha = 1.f;
   int force_bn = 0;
+  int no_tma_store = 0;  // debug: force the direct-store epilogue
 };
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream);
 void gemm_clear_tensor_map_cache();
+void gemm_set_trace(unsigned long long* dev_ptr);  // debug: per-CTA phase time stamps (8 x u64 per CTA), null to disable
 
 // ---- attention (fused, masks derived in-tile from token ids; transformer_model.py:73-109,350-363)
 struct AttnArgs {
