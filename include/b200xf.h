@@ -143,6 +143,17 @@ int b200xf_layernorm_residual_bwd(const void* dy, const void* z, const float* me
                                   void* dz, float* dgamma, float* dbeta, float* dcol, int rows, int d, void* scratch,
                                   void* stream);
 
+/* LayerNorm backward for callers that cannot allocate device memory (no counterpart in the reference).
+ * Identical results to b200xf_layernorm_residual_bwd, but the partial sums live in a fixed 3 637 248-byte array inside the
+ * library image instead of caller scratch, and the call allocates nothing.  Meant for an op hosted by a framework whose
+ * memory pool already owns the GPU (TensorFlow's default), or a loop that must not hit cudaMalloc's device-wide sync.
+ * Refused (error, nothing launched) when b200xf_layernorm_bwd_scratch_bytes(rows, d) exceeds that size; any rows with
+ * d <= 1024 fit.  The first call on a device resolves the array's address: make it before any stream capture, with that
+ * device current.  Calls share the array, so calls that overlap on the GPU race; nothing in it needs clearing. */
+int b200xf_layernorm_residual_bwd_noalloc(const void* dy, const void* z, const float* mean, const float* rstd,
+                                          const float* gamma, void* dz, float* dgamma, float* dbeta, float* dcol, int rows,
+                                          int d, void* stream);
+
 /* Embedding lookup * sqrt(d) + positional encoding (transformer_model.py:273-275,305-307) and its gradient. */
 int b200xf_embed_pe_fwd(const int64_t* tokens, const float* table, int vocab, const float* pe, void* out, int B, int S,
                         int d, void* stream);

@@ -68,6 +68,7 @@ SIGNATURES = {
     "b200xf_layernorm_residual_fwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _F, _P]),
     "b200xf_layernorm_bwd_scratch_bytes": (_SZ, [_I, _I]),
     "b200xf_layernorm_residual_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P]),
+    "b200xf_layernorm_residual_bwd_noalloc": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P]),
     "b200xf_embed_pe_fwd": (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _P]),
     "b200xf_embed_bwd_scratch_bytes": (_SZ, [_I]),
     "b200xf_embed_pe_bwd": (_I, [_P, _P, _P, _I, _I, _I, _P, _SZ, _P]),

@@ -3,6 +3,8 @@
 // the warm-up schedule over flat buckets, column sums (bias gradients), casts.
 // All global accesses are 128-bit vectorised and coalesced; reductions use warp shuffles.
 #include <algorithm>
+#include <mutex>
+
 #include <cub/device/device_radix_sort.cuh>
 
 #include "internal.h"
@@ -684,3 +686,62 @@ int cast_bf16_to_f32_2d(const bf16* in, int ldi, float* out, int ldo, int rows, 
 }
 
 }  // namespace b200xf
+
+// ============================================================================ LayerNorm backward without caller scratch
+// b200xf_layernorm_residual_bwd needs a scratch buffer for its per-block partial column sums, which normally means the
+// caller allocates device memory.  Some callers cannot: an op hosted by a framework that has already handed the whole
+// GPU to its own memory pool (TensorFlow's default allocator does this, and a C library underneath it cannot reach that
+// pool), or a steady-state loop that must never run into cudaMalloc's device-wide synchronisation.  For them the
+// variant below keeps the partials in a fixed array that is part of the loaded library image.
+namespace b200xf {
+namespace {
+// Capacity: 2 blocks per SM on a 148-SM part (296 blocks) x 3 sums x d <= 1024 columns = 909 312 floats (3.47 MiB).
+// Every GPU that loads the library carries this array until the process exits.
+constexpr size_t kStaticLnScratchFloats = size_t(296) * 3 * 1024;
+static __device__ __align__(256) float g_ln_bwd_static_scratch[kStaticLnScratchFloats];
+
+// In host code `g_ln_bwd_static_scratch` is only a handle for the symbol, not a device address, so the address the
+// kernels need is looked up once per device (with that device current) and remembered.
+int static_ln_scratch(float** out) {
+  static std::mutex mu;
+  static float* per_device[64] = {nullptr};
+  int dev = 0;
+  B200XF_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return set_error("device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!per_device[dev]) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_ln_bwd_static_scratch);
+    if (e != cudaSuccess || !p) return set_error("cudaGetSymbolAddress(static LayerNorm scratch): %s", cudaGetErrorString(e));
+    per_device[dev] = p;
+  }
+  *out = per_device[dev];
+  return 0;
+}
+}  // namespace
+}  // namespace b200xf
+
+// Same results as b200xf_layernorm_residual_bwd (same kernels, same summation order), no scratch argument and no
+// allocation of any kind: no cudaMalloc / cudaFree, no allocating library call.
+//  * Limit: b200xf_layernorm_bwd_scratch_bytes(rows, d) must not exceed 3 637 248 bytes (909 312 floats); that covers every
+//    row count for d <= 1024.  Larger problems are refused with an error, nothing is launched.
+//  * The first call on each device looks the array's address up (cudaGetSymbolAddress) with that device current; make that
+//    first call outside any stream capture.  `stream` must belong to the current device.
+//  * All calls on a device share the one array and it keeps whatever the previous call left in it.  Nothing in it has to be
+//    zero beforehand: each call first overwrites every partial slot it will later read.  For the same reason two calls that
+//    overlap on the GPU (different streams, or a second thread) race on it — serialise them.
+extern "C" int b200xf_layernorm_residual_bwd_noalloc(const void* dy, const void* z, const float* mean, const float* rstd,
+                                                     const float* gamma, void* dz, float* dgamma, float* dbeta, float* dcol,
+                                                     int rows, int d, void* stream) {
+  using namespace b200xf;
+  if (!dy || !z || !mean || !rstd || !gamma || !dz || !dgamma || !dbeta) return set_error("layernorm_bwd_noalloc: null pointer");
+  if (rows <= 0 || d <= 0 || d % 8 || d > 2048) return set_error("layernorm_bwd_noalloc: rows=%d d=%d unsupported (d multiple of 8, <= 2048)", rows, d);
+  const size_t need = ln_bwd_scratch_floats(rows, d);
+  if (need > kStaticLnScratchFloats)
+    return set_error("layernorm_bwd_noalloc: rows=%d d=%d needs %zu bytes of scratch, the built-in buffer holds %zu; use "
+                     "b200xf_layernorm_residual_bwd with caller scratch", rows, d, need * sizeof(float), kStaticLnScratchFloats * sizeof(float));
+  float* scratch = nullptr;
+  B200XF_TRY(static_ln_scratch(&scratch));
+  return layernorm_bwd(static_cast<const bf16*>(dy), static_cast<const bf16*>(z), mean, rstd, gamma, static_cast<bf16*>(dz), dgamma,
+                       dbeta, dcol, rows, d, scratch, static_cast<cudaStream_t>(stream));
+}
