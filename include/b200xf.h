@@ -70,7 +70,7 @@ int b200xf_params_changed(b200xf_ctx* ctx);
 int b200xf_set_iterations(b200xf_ctx* ctx, int64_t iterations);
 int b200xf_get_iterations(b200xf_ctx* ctx, int64_t* iterations);
 
-/* ---- Transformer.call (transformer_model.py:335-348), training=False/True with dropout 0 ------------
+/* ---- Transformer.call (transformer_model.py:335-348); training != 0 enables dropout when droput_rate > 0 ------
  * inp [B,S], tgt_in [B,T] int64 DEVICE pointers; logits_out fp32 [B,T,V] DEVICE pointer or NULL. */
 int b200xf_forward(b200xf_ctx* ctx, const int64_t* inp, const int64_t* tgt_in, int B, int S, int T, int training,
                    float* logits_out);
@@ -94,6 +94,16 @@ int b200xf_eval_step_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* 
 int b200xf_forward_backward_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T_plus_1,
                                    int workers_count, float* out6);
 int b200xf_synchronize(b200xf_ctx* ctx);
+
+/* Dropout(rate) (transformer_model.py:190-191,223-225,268,299; applied at :196,202,232,238,244,276,308) is inverted
+ * dropout from a counter-based generator keyed by (seed, site, optimizer.iterations, element index): nothing is stored,
+ * the backward pass recomputes the same mask.  TensorFlow's random stream cannot be matched, so the checker reads the
+ * mask itself: b200xf_dropout_mask writes, for dropout site `site` at the CURRENT iterations value, a DEVICE fp32
+ * [rows, cols] array holding 1/(1-rate) where the element is kept and 0 where it is dropped.  Sites: 0 / 1 encoder /
+ * decoder embedding; 2+2l, 3+2l encoder layer l after attention / FFN; 2+2L+3l, +1, +2 decoder layer l after
+ * self-attention / cross-attention / FFN. */
+int b200xf_set_dropout_seed(b200xf_ctx* ctx, uint64_t seed);
+int b200xf_dropout_mask(b200xf_ctx* ctx, int site, int rows, int cols, float* out);
 
 /* ---- MultiWorkerMirroredStrategy's implicit SUM all-reduce (cluster/cluster.py:66; __main__.py:113-114,
  * 131-132): NCCL over NVLink, one rank per process/GPU.  unique_id is the 128-byte ncclUniqueId obtained

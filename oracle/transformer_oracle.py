@@ -173,8 +173,11 @@ class OracleTransformer:
                  input_vocabulary_size, target_vocabulary_size, maximum_input_length,
                  maximum_target_length, droput_rate=0.0, emulate_bf16=False):
         assert embedding_size % heads_count == 0  # transformer_model.py:117
-        if droput_rate != 0.0:
-            raise ValueError("oracle covers dropout rate 0 only (BASELINE.json parity definition)")
+        # Dropout (transformer_model.py:190-191,223-225,268,299): TF's random stream cannot be reproduced, so with
+        # rate > 0 the caller supplies the masks (values 1/(1-rate) or 0) per site in `dropout_masks`
+        # {site id: [tokens, d] tensor}; site ids as in include/b200xf.h.  Without masks training=True is the identity.
+        self.droput_rate = droput_rate
+        self.dropout_masks = {}
         self.L, self.d, self.H, self.dff = layers_count, embedding_size, heads_count, feed_forward_hidden_size
         self.vin, self.vtgt = input_vocabulary_size, target_vocabulary_size
         self.pe_in = positional_encoding(maximum_input_length, embedding_size)
@@ -236,33 +239,42 @@ class OracleTransformer:
     def _ln(self, x, prefix):
         return self._layernorm(x, self.params[prefix + "/gamma"], self.params[prefix + "/beta"])
 
-    def encoder(self, tokens, mask):
+    def _drop(self, x, site, training):
+        """tf.keras.layers.Dropout with an externally supplied mask (see __init__)."""
+        if not training or site not in self.dropout_masks:
+            return x
+        return x * self.dropout_masks[site].reshape(x.shape)
+
+    def encoder(self, tokens, mask, training=False):
         """transformer_model.py:270-279."""
         S = tokens.shape[1]
         x = self.params["encoder/embedding/embeddings"][tokens]
         x = x * math.sqrt(float(self.d))
         x = x + self.pe_in[:, :S, :]
+        x = self._drop(x, 0, training)                                                    # :276
         for i in range(self.L):
             p = f"encoder/encoder_layers/{i}"
-            a, _ = self._mha(x, x, x, mask, p + "/mha")             # :195
-            o1 = self._ln(x + a, p + "/layernorm1")                  # :198
-            x = self._ln(o1 + self._ffn(o1, p), p + "/layernorm2")  # :201-204
+            a, _ = self._mha(x, x, x, mask, p + "/mha")                                   # :195
+            o1 = self._ln(x + self._drop(a, 2 + 2 * i, training), p + "/layernorm1")      # :196-198
+            x = self._ln(o1 + self._drop(self._ffn(o1, p), 3 + 2 * i, training), p + "/layernorm2")  # :201-204
         return x
 
-    def decoder(self, tokens, enc_out, la_mask, pad_mask):
+    def decoder(self, tokens, enc_out, la_mask, pad_mask, training=False):
         """transformer_model.py:301-315."""
         T = tokens.shape[1]
         weights = {}
         x = self.params["decoder/embedding/embeddings"][tokens]
         x = x * math.sqrt(float(self.d))
         x = x + self.pe_tgt[:, :T, :]
+        x = self._drop(x, 1, training)                                                # :308
+        base = 2 + 2 * self.L
         for i in range(self.L):
             p = f"decoder/decoder_layers/{i}"
             a1, w1 = self._mha(x, x, x, la_mask, p + "/mha1")                       # :230
-            o1 = self._ln(a1 + x, p + "/layernorm1")                                  # :233
+            o1 = self._ln(self._drop(a1, base + 3 * i, training) + x, p + "/layernorm1")              # :232-233
             a2, w2 = self._mha(enc_out, enc_out, o1, pad_mask, p + "/mha2")          # :236-237
-            o2 = self._ln(a2 + o1, p + "/layernorm2")                                 # :240
-            x = self._ln(self._ffn(o2, p) + o2, p + "/layernorm3")                   # :243-246
+            o2 = self._ln(self._drop(a2, base + 3 * i + 1, training) + o1, p + "/layernorm2")         # :238-240
+            x = self._ln(self._drop(self._ffn(o2, p), base + 3 * i + 2, training) + o2, p + "/layernorm3")  # :243-246
             weights[f"decoder_layer{i+1}_block1"] = w1
             weights[f"decoder_layer{i+1}_block2"] = w2
         return x, weights
@@ -271,8 +283,8 @@ class OracleTransformer:
         """transformer_model.py:335-348 — returns (logits [B,T,V], attention-weights dict)."""
         inp, tgt = inputs
         enc_mask, la_mask, dec_mask = create_masks(inp, tgt)
-        enc_out = self.encoder(inp, enc_mask)
-        dec_out, w = self.decoder(tgt, enc_out, la_mask, dec_mask)
+        enc_out = self.encoder(inp, enc_mask, training)
+        dec_out, w = self.decoder(tgt, enc_out, la_mask, dec_mask, training)
         return self._dense(dec_out, "final_layer"), w
 
 

@@ -57,6 +57,8 @@ SIGNATURES = {
     "b200xf_eval_step_device": (_I, [_P, _P, _P, _I, _I, _I, _P]),
     "b200xf_forward_backward_device": (_I, [_P, _P, _P, _I, _I, _I, _I, _P]),
     "b200xf_synchronize": (_I, [_P]),
+    "b200xf_set_dropout_seed": (_I, [_P, C.c_uint64]),
+    "b200xf_dropout_mask": (_I, [_P, _I, _I, _I, _P]),
     "b200xf_comm_unique_id": (_I, [_P]),
     "b200xf_comm_init": (_I, [_P, _P, _I, _I]),
     "b200xf_comm_destroy": (_I, [_P]),

@@ -50,10 +50,9 @@ int b200xf_get_iterations(b200xf_ctx* ctx, int64_t* it) {
 }
 
 int b200xf_forward(b200xf_ctx* ctx, const int64_t* inp, const int64_t* tgt_in, int B, int S, int T, int training, float* logits_out) {
-  (void)training;
   if (!ctx || !inp || !tgt_in) return set_error("null argument");
   if (cudaSetDevice(ctx->c.device) != cudaSuccess) return set_error("cudaSetDevice failed");
-  return ctx->c.forward(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(tgt_in), B, S, T, logits_out);
+  return ctx->c.forward(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(tgt_in), B, S, T, logits_out, training != 0);
 }
 int b200xf_train_step_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T1, int workers, float* out6) {
   if (!ctx || !inp || !target) return set_error("null argument");
@@ -70,6 +69,21 @@ int b200xf_eval_step_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* 
 int b200xf_forward_backward_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T1, int workers, float* out6) {
   if (!ctx || !inp || !target) return set_error("null argument");
   return ctx->c.step_device(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(target), B, S, T1, workers, 1, out6);
+}
+int b200xf_set_dropout_seed(b200xf_ctx* ctx, uint64_t seed) {
+  if (!ctx) return set_error("null ctx");
+  ctx->c.dropout_seed = seed;
+  return 0;
+}
+int b200xf_dropout_mask(b200xf_ctx* ctx, int site, int rows, int cols, float* out) {
+  if (!ctx || !out) return set_error("null argument");
+  Context& c = ctx->c;
+  const bool saved = c.dropout_on;
+  c.dropout_on = c.hp.droput_rate > 0.f;
+  const DropArgs d = c.site_drop(site);
+  c.dropout_on = saved;
+  if (!d.thresh) return set_error("dropout is disabled (rate 0)");
+  return dropout_mask_fill(out, rows, cols, d, c.stream);
 }
 int b200xf_synchronize(b200xf_ctx* ctx) {
   if (!ctx) return set_error("null ctx");

@@ -219,7 +219,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   const int dk = d / H;
   if (dk != 16 && dk != 32 && dk != 64) return set_error("head size %d unsupported (16, 32 or 64)", dk);
   if (d % 8 || dff % 8 || d > 2048) return set_error("embedding_size and feed_forward_hidden_size must be multiples of 8 (d <= 2048)");
-  if (hp.droput_rate != 0.f) return set_error("dropout rate %g: only rate 0 is implemented in this build", hp.droput_rate);
+  if (!(hp.droput_rate >= 0.f && hp.droput_rate < 1.f)) return set_error("dropout rate %g must be in [0, 1)", hp.droput_rate);
   if (hp.max_tokens <= 0) return set_error("max_tokens must be positive");
   B200XF_CUDA(cudaSetDevice(device));
   build_layout();
@@ -259,7 +259,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   for (int l = 0; l < L; ++l) { need(3 * nd, 2); for (int i = 0; i < 8; ++i) need(nd, 2); need(nff, 2); need(4 * N * H, 4); need(6 * N, 4); }
   need(N * size_t(L) * 2 * d, 2); need(N * size_t(L) * 2 * d, 2);   // kv_all, dkv_all
   need(N * size_t(vt_ld), 2);                                       // logits / dlogits
-  for (int i = 0; i < 5; ++i) need(nd, 2);                          // dA dB dz dctx dq2
+  for (int i = 0; i < 6; ++i) need(nd, 2);                          // dA dB dz dzm dctx dq2
   need(nff, 2); need(3 * nd, 2);                                    // dh dqkv
   need(N * H, 4);                                                   // delta
   for (int i = 0; i < 4; ++i) need(N + 64, 8);                      // inp, target, tgt_in, labels
@@ -293,7 +293,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   B200XF_TRY(arena_alloc(&kv, N * size_t(L) * 2 * d)); B200XF_TRY(arena_alloc(&dkv, N * size_t(L) * 2 * d));
   B200XF_TRY(arena_alloc(&logits, N * size_t(vt_ld)));
   B200XF_TRY(arena_alloc(&dA, nd)); B200XF_TRY(arena_alloc(&dB, nd)); B200XF_TRY(arena_alloc(&dz, nd));
-  B200XF_TRY(arena_alloc(&dctx, nd)); B200XF_TRY(arena_alloc(&dq2, nd));
+  B200XF_TRY(arena_alloc(&dctx, nd)); B200XF_TRY(arena_alloc(&dq2, nd)); B200XF_TRY(arena_alloc(&dzm, nd));
   B200XF_TRY(arena_alloc(&dh, nff)); B200XF_TRY(arena_alloc(&dqkv, 3 * nd));
   B200XF_TRY(arena_alloc(&delta, N * H));
   B200XF_TRY(arena_alloc(&tok_inp, N + 64)); B200XF_TRY(arena_alloc(&tok_target, N + 64));
@@ -384,8 +384,22 @@ int Context::allreduce(float* ptr, size_t count, cudaStream_t s) {
   return 0;
 }
 
+// ------------------------------------------------------------------------------------ dropout sites
+// site ids: 0 encoder embedding, 1 decoder embedding, 2+2l / 3+2l encoder layer l after MHA / FFN,
+// 2+2L+3l.. decoder layer l after MHA1 / MHA2 / FFN (transformer_model.py:196,202,232,238,244,276,308).
+DropArgs Context::site_drop(int site) const {
+  DropArgs d;
+  if (!dropout_on) return d;
+  d.step = iterations_dev;
+  d.key = (dropout_seed * 0x9E3779B97F4A7C15ull) ^ (static_cast<unsigned long long>(site + 1) * 0xC2B2AE3D27D4EB4Full);
+  const double t = double(hp.droput_rate) * 4294967296.0;
+  d.thresh = t >= 4294967295.0 ? 4294967295u : static_cast<unsigned>(t);
+  d.scale = 1.0f / (1.0f - hp.droput_rate);
+  return d;
+}
+
 // ------------------------------------------------------------------------------------ GEMM helpers
-int Context::dense_fwd(const bf16* x, int M, const Dense& p, bf16* y, int relu, const bf16* resid) {
+int Context::dense_fwd(const bf16* x, int M, const Dense& p, bf16* y, int relu, const bf16* resid, int drop_site) {
   GemmArgs g;
   g.a = x; g.lda = p.K; g.a_mn = 0;
   g.b = shadow + p.w; g.ldb = p.ld; g.b_mn = 1;
@@ -393,6 +407,7 @@ int Context::dense_fwd(const bf16* x, int M, const Dense& p, bf16* y, int relu, 
   g.M = M; g.N = p.N; g.K = p.K;
   g.bias = params + p.b; g.relu = relu;
   g.resid = resid; g.ldr = p.ld; g.resid_op = resid ? 1 : 0;
+  if (drop_site >= 0) g.drop = site_drop(drop_site);
   return gemm_bf16(g, stream);
 }
 int Context::dense_dgrad(const bf16* dy, int M, const Dense& p, bf16* dx, const bf16* resid, int resid_op) {
@@ -423,15 +438,16 @@ int Context::check_shapes(int B, int S, int T) {
   return 0;
 }
 
-int Context::forward(const long long* inp, const long long* tgt_in, int B, int S, int T, float* logits_f32) {
+int Context::forward(const long long* inp, const long long* tgt_in, int B, int S, int T, float* logits_f32, bool training) {
   B200XF_TRY(check_shapes(B, S, T));
+  dropout_on = training && hp.droput_rate > 0.f;
   const int L = hp.layers_count, d = hp.embedding_size, H = hp.heads_count, dk = d / H;
   const int Ns = B * S, Nt = B * T;
   const size_t cap = size_t(hp.max_tokens) * d;
   const float eps = 1e-6f;  // transformer_model.py:187-188
 
   // ---- encoder (transformer_model.py:270-279)
-  B200XF_TRY(embed_pe_fwd(inp, params + enc_emb, hp.input_vocabulary_size, pe_in, enc_x, B, S, d, stream));
+  B200XF_TRY(embed_pe_fwd(inp, params + enc_emb, hp.input_vocabulary_size, pe_in, enc_x, B, S, d, stream, site_drop(0)));
   for (int l = 0; l < L; ++l) {
     const EncLayer& w = enc[l]; EncAct& a = ea[l];
     const bf16* x = enc_x + size_t(l) * cap; bf16* out = enc_x + size_t(l + 1) * cap;
@@ -442,17 +458,17 @@ int Context::forward(const long long* inp, const long long* tgt_in, int B, int S
     at.o = a.ctx; at.ldo = d; at.lse = a.lse; at.key_tokens = inp; at.causal = 0;
     at.B = B; at.H = H; at.Sq = S; at.Sk = S; at.dk = dk;
     B200XF_TRY(attention_fwd(at, stream));
-    B200XF_TRY(dense_fwd(a.ctx, Ns, w.o, a.z1, 0, x));                                   // z1 = x + mha(x)
+    B200XF_TRY(dense_fwd(a.ctx, Ns, w.o, a.z1, 0, x, 2 + 2 * l));                        // z1 = x + drop(mha(x))
     B200XF_TRY(layernorm_fwd(a.z1, nullptr, params + w.ln1.g, params + w.ln1.b, a.o1, nullptr, st, st + Ns, Ns, d, eps, stream));
     B200XF_TRY(dense_fwd(a.o1, Ns, w.f1, a.h, 1, nullptr));
-    B200XF_TRY(dense_fwd(a.h, Ns, w.f2, a.z2, 0, a.o1));                                 // z2 = o1 + ffn(o1)
+    B200XF_TRY(dense_fwd(a.h, Ns, w.f2, a.z2, 0, a.o1, 3 + 2 * l));                      // z2 = o1 + drop(ffn(o1))
     B200XF_TRY(layernorm_fwd(a.z2, nullptr, params + w.ln2.g, params + w.ln2.b, out, nullptr, st + 2 * Ns, st + 3 * Ns, Ns, d, eps, stream));
   }
   const bf16* enc_out = enc_x + size_t(L) * cap;
   B200XF_TRY(dense_fwd(enc_out, Ns, kv_all, kv, 0, nullptr));  // K|V of every decoder layer's cross-attention
 
   // ---- decoder (transformer_model.py:301-315)
-  B200XF_TRY(embed_pe_fwd(tgt_in, params + dec_emb, hp.target_vocabulary_size, pe_tgt, dec_x, B, T, d, stream));
+  B200XF_TRY(embed_pe_fwd(tgt_in, params + dec_emb, hp.target_vocabulary_size, pe_tgt, dec_x, B, T, d, stream, site_drop(1)));
   for (int l = 0; l < L; ++l) {
     const DecLayer& w = dec[l]; DecAct& a = da[l];
     const bf16* x = dec_x + size_t(l) * cap; bf16* out = dec_x + size_t(l + 1) * cap;
@@ -463,7 +479,7 @@ int Context::forward(const long long* inp, const long long* tgt_in, int B, int S
     s1.o = a.ctx1; s1.ldo = d; s1.lse = a.lse1; s1.key_tokens = tgt_in; s1.causal = 1;
     s1.B = B; s1.H = H; s1.Sq = T; s1.Sk = T; s1.dk = dk;
     B200XF_TRY(attention_fwd(s1, stream));
-    B200XF_TRY(dense_fwd(a.ctx1, Nt, w.o1, a.z1, 0, x));
+    B200XF_TRY(dense_fwd(a.ctx1, Nt, w.o1, a.z1, 0, x, 2 + 2 * L + 3 * l));
     B200XF_TRY(layernorm_fwd(a.z1, nullptr, params + w.ln1.g, params + w.ln1.b, a.o1, nullptr, st, st + Nt, Nt, d, eps, stream));
     B200XF_TRY(dense_fwd(a.o1, Nt, w.q2, a.q2, 0, nullptr));
     AttnArgs c2;
@@ -471,10 +487,10 @@ int Context::forward(const long long* inp, const long long* tgt_in, int B, int S
     c2.o = a.ctx2; c2.ldo = d; c2.lse = a.lse2; c2.key_tokens = inp; c2.causal = 0;
     c2.B = B; c2.H = H; c2.Sq = T; c2.Sk = S; c2.dk = dk;
     B200XF_TRY(attention_fwd(c2, stream));
-    B200XF_TRY(dense_fwd(a.ctx2, Nt, w.o2, a.z2, 0, a.o1));
+    B200XF_TRY(dense_fwd(a.ctx2, Nt, w.o2, a.z2, 0, a.o1, 3 + 2 * L + 3 * l));
     B200XF_TRY(layernorm_fwd(a.z2, nullptr, params + w.ln2.g, params + w.ln2.b, a.o2, nullptr, st + 2 * Nt, st + 3 * Nt, Nt, d, eps, stream));
     B200XF_TRY(dense_fwd(a.o2, Nt, w.f1, a.h, 1, nullptr));
-    B200XF_TRY(dense_fwd(a.h, Nt, w.f2, a.z3, 0, a.o2));
+    B200XF_TRY(dense_fwd(a.h, Nt, w.f2, a.z3, 0, a.o2, 4 + 2 * L + 3 * l));
     B200XF_TRY(layernorm_fwd(a.z3, nullptr, params + w.ln3.g, params + w.ln3.b, out, nullptr, st + 4 * Nt, st + 5 * Nt, Nt, d, eps, stream));
   }
   const bf16* dec_out = dec_x + size_t(L) * cap;
@@ -501,12 +517,14 @@ float* Context::red_alloc(size_t floats) {
 }
 
 int Context::ln_bwd(const bf16* dy, const bf16* z, const float* st_mean, const float* st_rstd, const LnP& p, size_t dcol_off,
-                    int rows) {
+                    int rows, int drop_site) {
   const int d = hp.embedding_size;
   const int n = ln_bwd_parts(rows);
   float* part = red_alloc(size_t(n) * 3 * d);
   if (!part) return set_error("reduction scratch exhausted");
-  B200XF_TRY(layernorm_bwd_partial(dy, z, st_mean, st_rstd, params + p.g, dz, rows, d, part, stream));
+  const DropArgs drop = site_drop(drop_site);
+  dsub = drop.thresh ? dzm : dz;  // what the Dense that fed this residual sees
+  B200XF_TRY(layernorm_bwd_partial(dy, z, st_mean, st_rstd, params + p.g, dz, rows, d, part, stream, dzm, drop));
   red_jobs.push_back({part, grads + p.g, n, d, 3 * d});
   red_jobs.push_back({part + d, grads + p.b, n, d, 3 * d});
   red_jobs.push_back({part + 2 * d, grads + dcol_off, n, d, 3 * d});
@@ -552,17 +570,17 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     const bf16* x = dec_x + size_t(l) * cap;
     float* st = a.stats;
     // LN3 / FFN
-    B200XF_TRY(ln_bwd(cur, a.z3, st + 4 * Nt, st + 5 * Nt, w.ln3, w.f2.b, Nt));
-    B200XF_TRY(dense_wgrad(a.h, dz, Nt, w.f2));
-    B200XF_TRY(dense_dgrad(dz, Nt, w.f2, dh, a.h, 2));
+    B200XF_TRY(ln_bwd(cur, a.z3, st + 4 * Nt, st + 5 * Nt, w.ln3, w.f2.b, Nt, 4 + 2 * L + 3 * l));
+    B200XF_TRY(dense_wgrad(a.h, dsub, Nt, w.f2));
+    B200XF_TRY(dense_dgrad(dsub, Nt, w.f2, dh, a.h, 2));
     B200XF_TRY(colsum(dh, w.f1.ld, Nt, w.f1.N, w.f1.b));
     B200XF_TRY(dense_wgrad(a.o2, dh, Nt, w.f1));
     B200XF_TRY(dense_dgrad(dh, Nt, w.f1, other, dz, 1));
     std::swap(cur, other);
     // LN2 / cross attention
-    B200XF_TRY(ln_bwd(cur, a.z2, st + 2 * Nt, st + 3 * Nt, w.ln2, w.o2.b, Nt));
-    B200XF_TRY(dense_wgrad(a.ctx2, dz, Nt, w.o2));
-    B200XF_TRY(dense_dgrad(dz, Nt, w.o2, dctx, nullptr, 0));
+    B200XF_TRY(ln_bwd(cur, a.z2, st + 2 * Nt, st + 3 * Nt, w.ln2, w.o2.b, Nt, 3 + 2 * L + 3 * l));
+    B200XF_TRY(dense_wgrad(a.ctx2, dsub, Nt, w.o2));
+    B200XF_TRY(dense_dgrad(dsub, Nt, w.o2, dctx, nullptr, 0));
     AttnArgs c2;
     c2.q = a.q2; c2.ldq = d; c2.k = kv + size_t(l) * 2 * d; c2.v = kv + size_t(l) * 2 * d + d; c2.ldk = c2.ldv = kv_all.ld;
     c2.o = a.ctx2; c2.ldo = d; c2.lse = a.lse2; c2.key_tokens = inp; c2.causal = 0;
@@ -575,9 +593,9 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     B200XF_TRY(dense_dgrad(dq2, Nt, w.q2, other, dz, 1));
     std::swap(cur, other);
     // LN1 / causal self attention
-    B200XF_TRY(ln_bwd(cur, a.z1, st, st + Nt, w.ln1, w.o1.b, Nt));
-    B200XF_TRY(dense_wgrad(a.ctx1, dz, Nt, w.o1));
-    B200XF_TRY(dense_dgrad(dz, Nt, w.o1, dctx, nullptr, 0));
+    B200XF_TRY(ln_bwd(cur, a.z1, st, st + Nt, w.ln1, w.o1.b, Nt, 2 + 2 * L + 3 * l));
+    B200XF_TRY(dense_wgrad(a.ctx1, dsub, Nt, w.o1));
+    B200XF_TRY(dense_dgrad(dsub, Nt, w.o1, dctx, nullptr, 0));
     AttnArgs s1;
     s1.q = a.qkv; s1.k = a.qkv + d; s1.v = a.qkv + 2 * d; s1.ldq = s1.ldk = s1.ldv = 3 * d;
     s1.o = a.ctx1; s1.ldo = d; s1.lse = a.lse1; s1.key_tokens = tgt_in; s1.causal = 1;
@@ -591,7 +609,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     std::swap(cur, other);
     B200XF_TRY(section_done());
   }
-  B200XF_TRY(embed_bwd(tgt_in, cur, grads + dec_emb, hp.target_vocabulary_size, Nt, d, emb_scratch, emb_scratch_bytes, stream));
+  B200XF_TRY(embed_bwd(tgt_in, cur, grads + dec_emb, hp.target_vocabulary_size, Nt, d, emb_scratch, emb_scratch_bytes, stream, site_drop(1)));
   const bf16* enc_out = enc_x + size_t(L) * cap;
   B200XF_TRY(colsum(dkv, kv_all.ld, Ns, kv_all.N, kv_all.b));
   B200XF_TRY(dense_wgrad(enc_out, dkv, Ns, kv_all));
@@ -602,16 +620,16 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     const EncLayer& w = enc[l]; EncAct& a = ea[l];
     const bf16* x = enc_x + size_t(l) * cap;
     float* st = a.stats;
-    B200XF_TRY(ln_bwd(cur, a.z2, st + 2 * Ns, st + 3 * Ns, w.ln2, w.f2.b, Ns));
-    B200XF_TRY(dense_wgrad(a.h, dz, Ns, w.f2));
-    B200XF_TRY(dense_dgrad(dz, Ns, w.f2, dh, a.h, 2));
+    B200XF_TRY(ln_bwd(cur, a.z2, st + 2 * Ns, st + 3 * Ns, w.ln2, w.f2.b, Ns, 3 + 2 * l));
+    B200XF_TRY(dense_wgrad(a.h, dsub, Ns, w.f2));
+    B200XF_TRY(dense_dgrad(dsub, Ns, w.f2, dh, a.h, 2));
     B200XF_TRY(colsum(dh, w.f1.ld, Ns, w.f1.N, w.f1.b));
     B200XF_TRY(dense_wgrad(a.o1, dh, Ns, w.f1));
     B200XF_TRY(dense_dgrad(dh, Ns, w.f1, other, dz, 1));
     std::swap(cur, other);
-    B200XF_TRY(ln_bwd(cur, a.z1, st, st + Ns, w.ln1, w.o.b, Ns));
-    B200XF_TRY(dense_wgrad(a.ctx, dz, Ns, w.o));
-    B200XF_TRY(dense_dgrad(dz, Ns, w.o, dctx, nullptr, 0));
+    B200XF_TRY(ln_bwd(cur, a.z1, st, st + Ns, w.ln1, w.o.b, Ns, 2 + 2 * l));
+    B200XF_TRY(dense_wgrad(a.ctx, dsub, Ns, w.o));
+    B200XF_TRY(dense_dgrad(dsub, Ns, w.o, dctx, nullptr, 0));
     AttnArgs at;
     at.q = a.qkv; at.k = a.qkv + d; at.v = a.qkv + 2 * d; at.ldq = at.ldk = at.ldv = 3 * d;
     at.o = a.ctx; at.ldo = d; at.lse = a.lse; at.key_tokens = inp; at.causal = 0;
@@ -625,7 +643,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     std::swap(cur, other);
     B200XF_TRY(section_done());
   }
-  B200XF_TRY(embed_bwd(inp, cur, grads + enc_emb, hp.input_vocabulary_size, Ns, d, emb_scratch, emb_scratch_bytes, stream));
+  B200XF_TRY(embed_bwd(inp, cur, grads + enc_emb, hp.input_vocabulary_size, Ns, d, emb_scratch, emb_scratch_bytes, stream, site_drop(0)));
   B200XF_TRY(section_done());
   B200XF_TRY(flush_reductions());
   return 0;
@@ -669,7 +687,7 @@ int Context::step_device(const long long* inp, const long long* target, int B, i
   if (workers_count <= 0) return set_error("workers_count must be positive");
   B200XF_CUDA(cudaSetDevice(device));
   B200XF_TRY(prep_targets(target, tok_tgt_in, tok_labels, nonpad_count, B, T1, stream));
-  B200XF_TRY(forward(inp, tok_tgt_in, B, S, T, nullptr));
+  B200XF_TRY(forward(inp, tok_tgt_in, B, S, T, nullptr, mode != 0));
   B200XF_TRY(loss_and_grad(B * T, workers_count, mode != 0));
   if (mode >= 1) {
     overlap_update = (mode == 2) && (comm != nullptr || overlap_single);

@@ -48,6 +48,8 @@ struct Context {
   char* arena = nullptr; size_t arena_size = 0, arena_used = 0;
   bf16 *enc_x = nullptr, *dec_x = nullptr, *kv = nullptr, *dkv = nullptr, *logits = nullptr;
   std::vector<EncAct> ea; std::vector<DecAct> da;
+  bool dropout_on = false; unsigned long long dropout_seed = 0x5EEDull;
+  bf16 *dzm = nullptr, *dsub = nullptr;
   bf16 *dA = nullptr, *dB = nullptr, *dz = nullptr, *dctx = nullptr, *dq2 = nullptr, *dh = nullptr, *dqkv = nullptr;
   float *delta = nullptr, *row_loss = nullptr, *red_scratch = nullptr, *pe_in = nullptr, *pe_tgt = nullptr, *metrics = nullptr;
   int *row_correct = nullptr, *nonpad_count = nullptr;
@@ -80,15 +82,16 @@ struct Context {
   int comm_destroy();
   int allreduce(float* ptr, size_t count, cudaStream_t s);
 
-  int dense_fwd(const bf16* x, int M, const Dense& p, bf16* y, int relu, const bf16* resid);
+  int dense_fwd(const bf16* x, int M, const Dense& p, bf16* y, int relu, const bf16* resid, int drop_site = -1);
+  DropArgs site_drop(int site) const;
   int dense_dgrad(const bf16* dy, int M, const Dense& p, bf16* dx, const bf16* resid, int resid_op);
   int dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p);
-  int ln_bwd(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const LnP& p, size_t dcol_off, int rows);
+  int ln_bwd(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const LnP& p, size_t dcol_off, int rows, int drop_site);
   int colsum(const bf16* x, int ld, int rows, int cols, size_t dst_off);
   float* red_alloc(size_t floats);
   int flush_reductions();
   int check_shapes(int B, int S, int T);
-  int forward(const long long* inp, const long long* tgt_in, int B, int S, int T, float* logits_f32);
+  int forward(const long long* inp, const long long* tgt_in, int B, int S, int T, float* logits_f32, bool training);
   int backward(const long long* inp, const long long* tgt_in, int B, int S, int T);
   int section_done();
   int loss_and_grad(int Nt, int workers_count, int write_grad);

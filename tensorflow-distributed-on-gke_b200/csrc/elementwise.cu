@@ -102,7 +102,7 @@ template <int CH>
 __global__ void __launch_bounds__(kLnWarps * 32)
 ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const float* __restrict__ mean_in,
               const float* __restrict__ rstd_in, const float* __restrict__ gamma, bf16* __restrict__ dz, int rows, int d,
-              float* __restrict__ partials) {
+              float* __restrict__ partials, bf16* __restrict__ dzm, const DropArgs drop) {
   extern __shared__ float red[];  // [3][d]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float gam[CH][8];
@@ -113,6 +113,7 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
 #pragma unroll
     for (int j = 0; j < 8; ++j) { acc_g[c][j] = acc_b[c][j] = acc_c[c][j] = 0.f; gam[c][j] = (col < d) ? __ldg(gamma + col + j) : 0.f; }
   }
+  const unsigned long long dstream = drop.thresh ? drop_stream(drop) : 0ull;
   // software pipeline: the next row's loads are issued before the current row's reductions
   uint4 nxt_dy[CH], nxt_z[CH];
   float nxt_mean = 0.f, nxt_rstd = 0.f;
@@ -160,8 +161,15 @@ ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const flo
       if (col < d) {
         float o[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { o[j] = rstd * (g[c][j] - m1 - xh[c][j] * m2); acc_c[c][j] += round_bf16(o[j]); }
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (g[c][j] - m1 - xh[c][j] * m2);
         *reinterpret_cast<uint4*>(dz + base + col) = pack8(o);
+        if (drop.thresh) {  // gradient seen by the Dense whose (dropped-out) output was added to the residual
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = drop_keep(dstream, base + col + j, drop.thresh) ? o[j] * drop.scale : 0.f;
+          *reinterpret_cast<uint4*>(dzm + base + col) = pack8(o);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc_c[c][j] += round_bf16(o[j]);
       }
     }
   }
@@ -236,13 +244,14 @@ int ln_bwd_parts(int rows) { return std::max(1, std::min((rows + kLnWarps - 1) /
 size_t ln_bwd_scratch_floats(int rows, int d) { return size_t(ln_bwd_parts(rows)) * 3 * d; }
 
 int layernorm_bwd_partial(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const float* gamma, bf16* dz, int rows,
-                          int d, float* partials, cudaStream_t stream) {
+                          int d, float* partials, cudaStream_t stream, bf16* dzm, DropArgs drop) {
+  if (drop.thresh && !dzm) return set_error("layernorm_bwd: dropout needs a dzm buffer");
   if (d % 8 || d > 2048) return set_error("layernorm: d=%d must be a multiple of 8 and <= 2048", d);
   if (rows <= 0) return set_error("layernorm_bwd: no rows");
   const int grid = ln_bwd_parts(rows);
   const int ch = (d + 255) / 256;
   const size_t smem = size_t(3) * d * sizeof(float);
-#define LN_BWD(CH) ln_bwd_kernel<CH><<<grid, kLnWarps * 32, smem, stream>>>(dy, z, mean, rstd, gamma, dz, rows, d, partials)
+#define LN_BWD(CH) ln_bwd_kernel<CH><<<grid, kLnWarps * 32, smem, stream>>>(dy, z, mean, rstd, gamma, dz, rows, d, partials, dzm, drop)
   if (ch <= 1) LN_BWD(1); else if (ch <= 2) LN_BWD(2); else if (ch <= 4) LN_BWD(4); else LN_BWD(8);
 #undef LN_BWD
   B200XF_CUDA(cudaGetLastError());
@@ -284,8 +293,9 @@ namespace {
 
 // x[b,s,:] = table[token] * sqrt(d) + pe[s]   (fp32 master rows gathered bit-exactly, output bf16)
 __global__ void embed_fwd_kernel(const long long* __restrict__ tokens, const float* __restrict__ table, int vocab,
-                                 const float* __restrict__ pe, bf16* __restrict__ out, int S, int d, float scale) {
+                                 const float* __restrict__ pe, bf16* __restrict__ out, int S, int d, float scale, const DropArgs drop) {
   const int n = blockIdx.x;
+  const unsigned long long dstream = drop.thresh ? drop_stream(drop) : 0ull;
   const long long tok = tokens[n];
   const bool ok = tok >= 0 && tok < vocab;  // out-of-range ids read as a zero row (TF GPU gather semantics)
   const float* row = table + size_t(ok ? tok : 0) * d;
@@ -295,8 +305,14 @@ __global__ void embed_fwd_kernel(const long long* __restrict__ tokens, const flo
     const float4 q = __ldg(reinterpret_cast<const float4*>(p + c));
     uint2 u;
     // two separately rounded fp32 ops, as `x *= sqrt(d); x += pe` in the reference (no FMA contraction)
-    u.x = ptx::pack_bf16x2(__fadd_rn(__fmul_rn(e.x, scale), q.x), __fadd_rn(__fmul_rn(e.y, scale), q.y));
-    u.y = ptx::pack_bf16x2(__fadd_rn(__fmul_rn(e.z, scale), q.z), __fadd_rn(__fmul_rn(e.w, scale), q.w));
+    float v[4] = {__fadd_rn(__fmul_rn(e.x, scale), q.x), __fadd_rn(__fmul_rn(e.y, scale), q.y),
+                  __fadd_rn(__fmul_rn(e.z, scale), q.z), __fadd_rn(__fmul_rn(e.w, scale), q.w)};
+    if (drop.thresh) {  // transformer_model.py:276,308
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = drop_keep(dstream, size_t(n) * d + c + j, drop.thresh) ? v[j] * drop.scale : 0.f;
+    }
+    u.x = ptx::pack_bf16x2(v[0], v[1]);
+    u.y = ptx::pack_bf16x2(v[2], v[3]);
     *reinterpret_cast<uint2*>(out + size_t(n) * d + c) = u;
   }
 }
@@ -312,8 +328,9 @@ __global__ void embed_keys_kernel(const long long* __restrict__ tokens, int* __r
 // One block per sorted position; the block at the head of a run of equal token ids sums that run's
 // gradient rows in sorted (= original position) order and writes the table row once: deterministic.
 __global__ void embed_bwd_kernel(const int* __restrict__ keys, const int* __restrict__ vals, const bf16* __restrict__ dx,
-                                 float* __restrict__ dtable, int n, int d, int vocab, float scale) {
+                                 float* __restrict__ dtable, int n, int d, int vocab, float scale, const DropArgs drop) {
   const int p = blockIdx.x;
+  const unsigned long long dstream = drop.thresh ? drop_stream(drop) : 0ull;
   const int key = keys[p];
   if (key >= vocab || (p > 0 && keys[p - 1] == key)) return;
   int end = p + 1;
@@ -321,8 +338,14 @@ __global__ void embed_bwd_kernel(const int* __restrict__ keys, const int* __rest
   for (int c = threadIdx.x * 4; c < d; c += blockDim.x * 4) {
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
     for (int q = p; q < end; ++q) {
-      const uint2 u = *reinterpret_cast<const uint2*>(dx + size_t(vals[q]) * d + c);
-      a0 += ptx::bf16_lo(u.x); a1 += ptx::bf16_hi(u.x); a2 += ptx::bf16_lo(u.y); a3 += ptx::bf16_hi(u.y);
+      const size_t pos = size_t(vals[q]) * d + c;
+      const uint2 u = *reinterpret_cast<const uint2*>(dx + pos);
+      float g0 = ptx::bf16_lo(u.x), g1 = ptx::bf16_hi(u.x), g2 = ptx::bf16_lo(u.y), g3 = ptx::bf16_hi(u.y);
+      if (drop.thresh) {
+        g0 = drop_keep(dstream, pos, drop.thresh) ? g0 * drop.scale : 0.f; g1 = drop_keep(dstream, pos + 1, drop.thresh) ? g1 * drop.scale : 0.f;
+        g2 = drop_keep(dstream, pos + 2, drop.thresh) ? g2 * drop.scale : 0.f; g3 = drop_keep(dstream, pos + 3, drop.thresh) ? g3 * drop.scale : 0.f;
+      }
+      a0 += g0; a1 += g1; a2 += g2; a3 += g3;
     }
     float4* dst = reinterpret_cast<float4*>(dtable + size_t(key) * d + c);
     float4 cur = *dst;
@@ -336,12 +359,12 @@ size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 }  // namespace
 
 int embed_pe_fwd(const long long* tokens, const float* table, int vocab, const float* pe, bf16* out, int B, int S, int d,
-                 cudaStream_t stream) {
+                 cudaStream_t stream, DropArgs drop) {
   if (d % 4) return set_error("embedding: d=%d must be a multiple of 4", d);
   const int n = B * S;
   if (n <= 0) return 0;
   const int threads = min(256, max(32, (d / 4 + 31) / 32 * 32));
-  embed_fwd_kernel<<<n, threads, 0, stream>>>(tokens, table, vocab, pe, out, S, d, sqrtf(float(d)));
+  embed_fwd_kernel<<<n, threads, 0, stream>>>(tokens, table, vocab, pe, out, S, d, sqrtf(float(d)), drop);
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;
@@ -354,7 +377,7 @@ size_t embed_bwd_scratch_bytes(int n) {
 }
 
 int embed_bwd(const long long* tokens, const bf16* dx, float* dtable, int vocab, int n, int d, void* scratch, size_t scratch_bytes,
-              cudaStream_t stream) {
+              cudaStream_t stream, DropArgs drop) {
   if (n <= 0) return 0;
   if (scratch_bytes < embed_bwd_scratch_bytes(n)) return set_error("embed_bwd: scratch too small");
   const size_t seg = align_up(size_t(n) * sizeof(int), 256);
@@ -370,9 +393,26 @@ int embed_bwd(const long long* tokens, const bf16* dx, float* dtable, int vocab,
   while ((1ll << bits) <= vocab) ++bits;
   B200XF_CUDA(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, n, 0, bits, stream));
   const int threads = min(256, max(32, (d / 4 + 31) / 32 * 32));
-  embed_bwd_kernel<<<n, threads, 0, stream>>>(keys_out, vals_out, dx, dtable, n, d, vocab, sqrtf(float(d)));
+  embed_bwd_kernel<<<n, threads, 0, stream>>>(keys_out, vals_out, dx, dtable, n, d, vocab, sqrtf(float(d)), drop);
   B200XF_CUDA(cudaGetLastError());
   count_launch(3);
+  return 0;
+}
+
+namespace {
+__global__ void dropout_mask_kernel(float* __restrict__ out, size_t n, const DropArgs drop) {
+  const unsigned long long dstream = drop_stream(drop);
+  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x)
+    out[i] = drop_keep(dstream, i, drop.thresh) ? drop.scale : 0.f;
+}
+}  // namespace
+
+int dropout_mask_fill(float* out, int rows, int cols, DropArgs drop, cudaStream_t stream) {
+  const size_t n = size_t(rows) * cols;
+  if (n == 0) return 0;
+  dropout_mask_kernel<<<int(std::min<size_t>((n + 255) / 256, 4096)), 256, 0, stream>>>(out, n, drop);
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
   return 0;
 }
 

@@ -51,6 +51,7 @@ struct GemmParams {
   const __nv_bfloat16* resid; int ldr; int resid_op;  // 0 none, 1 add, 2 relu-mask
   float alpha;
   unsigned long long* trace;  // debug: 8 globaltimer stamps per CTA (null in production)
+  DropArgs drop;
 };
 
 // bias add, ReLU, residual add / ReLU mask on 32 accumulator columns [col0, col0+32) of one output row.
@@ -71,6 +72,12 @@ __device__ __forceinline__ void epilogue_math(float* f, const GemmParams& p, int
   if (p.relu) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+  }
+  if (p.drop.thresh) {
+    const unsigned long long stream = drop_stream(p.drop);
+    const unsigned long long base = static_cast<unsigned long long>(row) * p.N + col0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = drop_keep(stream, base + j, p.drop.thresh) ? f[j] * p.drop.scale : 0.f;
   }
   if (p.resid_op && row_ok) {
     const __nv_bfloat16* rp = p.resid + size_t(row) * p.ldr + col0;
@@ -457,6 +464,7 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   p.resid = reinterpret_cast<const __nv_bfloat16*>(a.resid); p.ldr = a.ldr; p.resid_op = a.resid ? a.resid_op : 0;
   p.alpha = a.alpha;
   p.trace = g_gemm_trace;
+  p.drop = a.drop;
 
   CUtensorMap ta, tb;
   int rc;

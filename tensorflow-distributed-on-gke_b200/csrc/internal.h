@@ -6,6 +6,8 @@
 #include <cstddef>
 #include <cstdint>
 
+#include "ptx.cuh"
+
 namespace b200xf {
 
 typedef __nv_bfloat16 bf16;
@@ -42,6 +44,7 @@ struct GemmArgs {
   float alpha = 1.f;
   int force_bn = 0;
   int no_tma_store = 0;  // debug: force the direct-store epilogue
+  DropArgs drop;         // inverted dropout on (acc + bias) before the residual add (transformer_model.py:196,202,232,238,244)
 };
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream);
 void gemm_clear_tensor_map_cache();
@@ -78,18 +81,21 @@ int reduce_partials(const ReduceJob* jobs, int njobs, cudaStream_t stream);
 // dz = LN'(dy); partials [ln_bwd_parts(rows)][3][d] = per-block sums of (dy*xhat, dy, dz) -> dgamma, dbeta, colsum(dz).
 int ln_bwd_parts(int rows);
 size_t ln_bwd_scratch_floats(int rows, int d);
+// dzm (optional, with drop.thresh != 0): dz * dropout mask of the sub-layer output that was added to the residual — the
+// gradient the producing Dense sees; the third partial sum is then taken over dzm.
 int layernorm_bwd_partial(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const float* gamma, bf16* dz,
-                          int rows, int d, float* partials, cudaStream_t stream);
+                          int rows, int d, float* partials, cudaStream_t stream, bf16* dzm = nullptr, DropArgs drop = DropArgs());
 // convenience: partial + reduce; scratch holds ln_bwd_scratch_floats(rows, d) floats.  dcol may be null.
 int layernorm_bwd(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const float* gamma, bf16* dz,
                   float* dgamma, float* dbeta, float* dcol, int rows, int d, float* scratch, cudaStream_t stream);
 
 // ---- embedding * sqrt(d) + positional encoding (transformer_model.py:273-275,305-307)
 int embed_pe_fwd(const long long* tokens, const float* table, int vocab, const float* pe, bf16* out, int B, int S, int d,
-                 cudaStream_t stream);
+                 cudaStream_t stream, DropArgs drop = DropArgs());
 size_t embed_bwd_scratch_bytes(int n_tokens);
 int embed_bwd(const long long* tokens, const bf16* dx, float* dtable, int vocab, int n_tokens, int d, void* scratch,
-              size_t scratch_bytes, cudaStream_t stream);
+              size_t scratch_bytes, cudaStream_t stream, DropArgs drop = DropArgs());
+int dropout_mask_fill(float* out, int rows, int cols, DropArgs drop, cudaStream_t stream);  // out = scale or 0 per element (tests)
 
 // ---- targets: shift, count (__main__.py:106-107; transformer_model.py:12)
 int prep_targets(const long long* target, long long* tgt_in, long long* labels, int* nonpad_count, int B, int T_plus_1,

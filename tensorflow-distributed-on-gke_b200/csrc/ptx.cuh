@@ -138,4 +138,23 @@ __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v 
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); }
 
 }  // namespace ptx
+
+// ---------------------------------------------------------------- dropout (counter-based, recomputed in backward)
+// keep(element) = hash(key, element index) >= rate * 2^32, key = f(seed, site, optimizer step): no mask is stored.
+struct DropArgs {
+  const long long* step = nullptr;  // device pointer to optimizer.iterations (read in-kernel: graph-replay safe)
+  unsigned long long key = 0;       // seed mixed with the dropout site id
+  unsigned thresh = 0;              // rate * 2^32; 0 disables dropout
+  float scale = 1.f;                // 1 / (1 - rate)
+};
+__device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
+  x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
+  return x;
+}
+__device__ __forceinline__ unsigned long long drop_stream(const DropArgs& d) {
+  return mix64(d.key ^ (static_cast<unsigned long long>(*d.step) * 0x9E3779B97F4A7C15ull));
+}
+__device__ __forceinline__ bool drop_keep(unsigned long long stream, unsigned long long idx, unsigned thresh) {
+  return static_cast<unsigned>(mix64(stream + idx * 0xD1342543DE82EF95ull) >> 32) >= thresh;
+}
 }  // namespace b200xf

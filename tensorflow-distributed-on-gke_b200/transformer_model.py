@@ -260,8 +260,6 @@ class Transformer:
         """transformer_model.py:335-348 — returns (logits fp32 [B,T,V] on the device, attention_weights dict).
         The masks of create_masks are applied inside the attention kernels from the token ids."""
         inp, tgt = inputs
-        if training and self.hparams["droput_rate"] != 0.0:
-            raise NotImplementedError("training=True with droput_rate > 0 is not implemented in this build")
         inp = _cuda_tokens(inp, self.device); tgt = _cuda_tokens(tgt, self.device)
         B, S = inp.shape
         T = tgt.shape[1]
@@ -308,6 +306,19 @@ class Transformer:
 
     def forward_backward_device(self, inp, target, workers_count=1):
         return self._step(_lib.load().b200xf_forward_backward_device, inp, target, int(workers_count))
+
+    def set_dropout_seed(self, seed):
+        self._ensure_built()
+        check(_lib.load().b200xf_set_dropout_seed(self._ctx, int(seed)))
+
+    def dropout_mask(self, site, rows):
+        """The inverted-dropout mask (1/(1-rate) or 0) of dropout site `site` for the CURRENT iterations value, as a
+        device fp32 [rows, embedding_size] tensor (site numbering: include/b200xf.h).  For tests."""
+        self._ensure_built()
+        d = self.hparams["embedding_size"]
+        out = torch.empty((rows, d), device=self.device, dtype=torch.float32)
+        check(_lib.load().b200xf_dropout_mask(self._ctx, int(site), int(rows), d, ptr(out)))
+        return out
 
     def synchronize(self):
         if self._ctx is not None:

@@ -170,3 +170,51 @@ def test_variable_shapes_and_workspace_growth():
     assert model.iterations == 3
     with pytest.raises(b200xf.B200XFError):
         model([np.ones((1, 100), np.int64), np.ones((1, 4), np.int64)])  # longer than maximum_input_length
+
+
+def test_dropout_train_step_parity_with_injected_masks():
+    """droput_rate = 0.1 (the reference script's value, __main__.py:43): the CUDA path's masks are read back through
+    b200xf_dropout_mask and injected into the oracle, so forward, loss and every gradient can be compared exactly as
+    in the rate-0 tests; plus the statistics of the mask itself."""
+    hp = dict(SMALL, droput_rate=0.1)
+    model = b200xf.Transformer(**hp, seed=4)
+    oracle = O.OracleTransformer(**hp).load(model.get_weights_dict())
+    oracle16 = O.OracleTransformer(**hp, emulate_bf16=True).load(model.get_weights_dict())
+    B, S, T = 6, 24, 21
+    inp, tgt = b200xf.synthetic_batch(B, S, T + 1, hp["input_vocabulary_size"], hp["target_vocabulary_size"], seed=31, ragged=True)
+    model.iterations = 700; oracle.iterations = 700; oracle16.iterations = 700
+    L = hp["layers_count"]
+    masks = {}
+    for site in range(2 + 2 * L + 3 * L):
+        rows = B * S if (site == 0 or 2 <= site < 2 + 2 * L) else B * T
+        masks[site] = model.dropout_mask(site, rows).cpu()
+    keep = torch.cat([m.reshape(-1) for m in masks.values()])
+    assert set(torch.unique(keep).tolist()) == {0.0, float(np.float32(1.0) / (np.float32(1.0) - np.float32(0.1)))}
+    frac = float((keep == 0).float().mean())
+    assert abs(frac - 0.1) < 0.01, frac                                      # ~1e5 Bernoulli(0.1) draws: sigma ~ 1e-3
+    assert not torch.equal(masks[2], masks[3])                                # sites draw independent masks
+    oracle.dropout_masks = masks; oracle16.dropout_masks = masks
+    out = model.forward_backward_device(inp, tgt, 1).cpu().numpy()
+    grads = model.get_slot_dict("grad")
+    loss_ref, _, gref = O.train_step(oracle, inp, tgt, 1)
+    _, _, g16 = O.train_step(oracle16, inp, tgt, 1)
+    assert abs(out[0] - loss_ref) < 1e-2, (out[0], loss_ref)
+    names = [n for n in gref if not n.endswith("key_generator_weights/bias")]
+    cat = lambda g: np.concatenate([g[n].ravel() for n in names])
+    e, e16 = _rel(cat(grads), cat(gref)), _rel(cat(g16), cat(gref))
+    assert e < 6e-2 and e < 1.3 * e16 + 5e-3, (e, e16)                        # same rule as the rate-0 gradient test
+    # a different step draws a different mask; the same step reproduces it
+    m_again = model.dropout_mask(2, B * S).cpu()
+    assert torch.equal(m_again, masks[2])
+    model.iterations = 701
+    assert not torch.equal(model.dropout_mask(2, B * S).cpu(), masks[2])
+    # training=False ignores dropout (fresh oracle: the one above has meanwhile applied its Adam update)
+    model.iterations = 700
+    oracle = O.OracleTransformer(**hp).load(model.get_weights_dict()); oracle.dropout_masks = masks
+    lg_eval, _ = model([inp, tgt[:, :-1]], training=False)
+    ref_eval, _ = oracle([torch.tensor(inp), torch.tensor(tgt[:, :-1])], training=False)
+    assert _rel(lg_eval.cpu().numpy(), ref_eval.detach().numpy()) < 2e-2
+    lg_train, _ = model([inp, tgt[:, :-1]], training=True)
+    ref_train, _ = oracle([torch.tensor(inp), torch.tensor(tgt[:, :-1])], training=True)
+    assert _rel(lg_train.cpu().numpy(), ref_train.detach().numpy()) < 2e-2
+    assert _rel(lg_train.cpu().numpy(), lg_eval.cpu().numpy()) > 5e-2
