@@ -157,8 +157,8 @@ int b200xf_layernorm_residual_bwd(const void* dy, const void* z, const float* me
  * Identical results to b200xf_layernorm_residual_bwd, but the partial sums live in a fixed 3 637 248-byte array inside the
  * library image instead of caller scratch, and the call allocates nothing.  Meant for an op hosted by a framework whose
  * memory pool already owns the GPU (TensorFlow's default), or a loop that must not hit cudaMalloc's device-wide sync.
- * Refused (error, nothing launched) when b200xf_layernorm_bwd_scratch_bytes(rows, d) exceeds that size; any rows with
- * d <= 1024 fit.  The first call on a device resolves the array's address: make it before any stream capture, with that
+ * Refused (error, nothing launched) when b200xf_layernorm_bwd_scratch_bytes(rows, d) exceeds that size (it holds up to
+ * 9 472 rows at d = 512, 2 368 rows at d = 1024).  The first call on a device resolves the array's address: make it before any stream capture, with that
  * device current.  Calls share the array, so calls that overlap on the GPU race; nothing in it needs clearing. */
 int b200xf_layernorm_residual_bwd_noalloc(const void* dy, const void* z, const float* mean, const float* rstd,
                                           const float* gamma, void* dz, float* dgamma, float* dbeta, float* dcol, int rows,

@@ -519,7 +519,7 @@ float* Context::red_alloc(size_t floats) {
 int Context::ln_bwd(const bf16* dy, const bf16* z, const float* st_mean, const float* st_rstd, const LnP& p, size_t dcol_off,
                     int rows, int drop_site) {
   const int d = hp.embedding_size;
-  const int n = ln_bwd_parts(rows);
+  const int n = ln_bwd_parts(rows, d);
   float* part = red_alloc(size_t(n) * 3 * d);
   if (!part) return set_error("reduction scratch exhausted");
   const DropArgs drop = site_drop(drop_site);

@@ -4,6 +4,7 @@
 // All global accesses are 128-bit vectorised and coalesced; reductions use warp shuffles.
 #include <algorithm>
 #include <mutex>
+#include <set>
 
 #include <cub/device/device_radix_sort.cuh>
 
@@ -95,114 +96,133 @@ ln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ resid, const 
 }
 
 // Backward: dz = rstd * (g - mean(g) - xhat * mean(g*xhat)),  g = dy * gamma.
-// Column sums (dgamma, dbeta, colsum(dz)) are accumulated per lane across the block's rows, reduced across the
-// block's warps in shared memory in a fixed order and written as per-block partials [block][3][d]; a batched
-// reduce_partials launch sums them later in a fixed order (deterministic, no float atomics).
-template <int CH>
-__global__ void __launch_bounds__(kLnWarps * 32)
+// Latency-oriented: each warp owns RPW rows whose loads are all issued up front (no serial row loop); the block's
+// 8 warps then reduce their column sums (dy*xhat, dy, dz) through shared memory, all threads in parallel, and write
+// ONE partial [3][d] per block (8*RPW rows).  A batched reduce_partials launch sums the partials later in a fixed
+// order (deterministic, no float atomics).
+template <int CH, int RPW>
+__global__ void __launch_bounds__(kLnWarps * 32, (CH * RPW <= 4) ? 2 : 1)
 ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const float* __restrict__ mean_in,
               const float* __restrict__ rstd_in, const float* __restrict__ gamma, bf16* __restrict__ dz, int rows, int d,
               float* __restrict__ partials, bf16* __restrict__ dzm, const DropArgs drop) {
-  extern __shared__ float red[];  // [3][d]
+  extern __shared__ float red[];  // [kLnWarps][3][d]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row0 = (blockIdx.x * kLnWarps + warp) * RPW;
+  uint4 u_dy[RPW][CH], u_z[RPW][CH];
+  float mean[RPW], rstd[RPW];
+#pragma unroll
+  for (int r = 0; r < RPW; ++r) {
+    const int row = row0 + r;
+    mean[r] = 0.f; rstd[r] = 0.f;
+    if (row < rows) {
+      const size_t base = size_t(row) * d;
+#pragma unroll
+      for (int c = 0; c < CH; ++c) {
+        const int col = (c * 32 + lane) * 8;
+        if (col < d) { u_dy[r][c] = *reinterpret_cast<const uint4*>(dy + base + col); u_z[r][c] = *reinterpret_cast<const uint4*>(z + base + col); }
+      }
+      mean[r] = mean_in[row]; rstd[r] = rstd_in[row];
+    }
+  }
   float gam[CH][8];
-  float acc_g[CH][8], acc_b[CH][8], acc_c[CH][8];
 #pragma unroll
   for (int c = 0; c < CH; ++c) {
     const int col = (c * 32 + lane) * 8;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { acc_g[c][j] = acc_b[c][j] = acc_c[c][j] = 0.f; gam[c][j] = (col < d) ? __ldg(gamma + col + j) : 0.f; }
+    for (int j = 0; j < 8; ++j) gam[c][j] = 0.f;
+    if (col < d) {
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + col)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + col + 4));
+      gam[c][0] = g0.x; gam[c][1] = g0.y; gam[c][2] = g0.z; gam[c][3] = g0.w; gam[c][4] = g1.x; gam[c][5] = g1.y; gam[c][6] = g1.z; gam[c][7] = g1.w;
+    }
   }
   const unsigned long long dstream = drop.thresh ? drop_stream(drop) : 0ull;
-  // software pipeline: the next row's loads are issued before the current row's reductions
-  uint4 nxt_dy[CH], nxt_z[CH];
-  float nxt_mean = 0.f, nxt_rstd = 0.f;
-  auto fetch = [&](int row) {
-    const size_t base = size_t(row) * d;
+  float acc_g[CH][8], acc_b[CH][8], acc_c[CH][8];
 #pragma unroll
-    for (int c = 0; c < CH; ++c) {
-      const int col = (c * 32 + lane) * 8;
-      if (col < d) { nxt_dy[c] = *reinterpret_cast<const uint4*>(dy + base + col); nxt_z[c] = *reinterpret_cast<const uint4*>(z + base + col); }
-    }
-    nxt_mean = mean_in[row]; nxt_rstd = rstd_in[row];
-  };
-  const int row_first = blockIdx.x * kLnWarps + warp, row_step = gridDim.x * kLnWarps;
-  if (row_first < rows) fetch(row_first);
-  for (int row = row_first; row < rows; row += row_step) {
-    const size_t base = size_t(row) * d;
-    const float mean = nxt_mean, rstd = nxt_rstd;
-    uint4 cur_dy[CH], cur_z[CH];
+  for (int c = 0; c < CH; ++c)
 #pragma unroll
-    for (int c = 0; c < CH; ++c) { cur_dy[c] = nxt_dy[c]; cur_z[c] = nxt_z[c]; }
-    if (row + row_step < rows) fetch(row + row_step);
-    float xh[CH][8], g[CH][8];
-    float s1 = 0.f, s2 = 0.f;
+    for (int j = 0; j < 8; ++j) acc_g[c][j] = acc_b[c][j] = acc_c[c][j] = 0.f;
+
 #pragma unroll
-    for (int c = 0; c < CH; ++c) {
-      const int col = (c * 32 + lane) * 8;
-      if (col < d) {
-        float a[8], b[8];
-        unpack8(cur_dy[c], a);
-        unpack8(cur_z[c], b);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          xh[c][j] = (b[j] - mean) * rstd;
-          g[c][j] = a[j] * gam[c][j];
-          s1 += g[c][j]; s2 += g[c][j] * xh[c][j];
-          acc_g[c][j] += a[j] * xh[c][j];
-          acc_b[c][j] += a[j];
-        }
-      }
-    }
-    const float m1 = warp_sum(s1) / float(d), m2 = warp_sum(s2) / float(d);
-#pragma unroll
-    for (int c = 0; c < CH; ++c) {
-      const int col = (c * 32 + lane) * 8;
-      if (col < d) {
-        float o[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = rstd * (g[c][j] - m1 - xh[c][j] * m2);
-        *reinterpret_cast<uint4*>(dz + base + col) = pack8(o);
-        if (drop.thresh) {  // gradient seen by the Dense whose (dropped-out) output was added to the residual
-#pragma unroll
-          for (int j = 0; j < 8; ++j) o[j] = drop_keep(dstream, base + col + j, drop.thresh) ? o[j] * drop.scale : 0.f;
-          *reinterpret_cast<uint4*>(dzm + base + col) = pack8(o);
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc_c[c][j] += round_bf16(o[j]);
-      }
-    }
-  }
-  // block reduce: warps add into shared memory one after another (fixed order)
-  for (int i = threadIdx.x; i < 3 * d; i += blockDim.x) red[i] = 0.f;
-  __syncthreads();
-  for (int w = 0; w < kLnWarps; ++w) {
-    if (warp == w) {
+  for (int r = 0; r < RPW; ++r) {
+    const int row = row0 + r;
+    if (row < rows) {  // warp-uniform
+      const size_t base = size_t(row) * d;
+      float xh[CH][8], g[CH][8];
+      float s1 = 0.f, s2 = 0.f;
 #pragma unroll
       for (int c = 0; c < CH; ++c) {
         const int col = (c * 32 + lane) * 8;
         if (col < d) {
+          float a[8], b[8];
+          unpack8(u_dy[r][c], a);
+          unpack8(u_z[r][c], b);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) { red[col + j] += acc_g[c][j]; red[d + col + j] += acc_b[c][j]; red[2 * d + col + j] += acc_c[c][j]; }
+          for (int j = 0; j < 8; ++j) {
+            xh[c][j] = (b[j] - mean[r]) * rstd[r];
+            g[c][j] = a[j] * gam[c][j];
+            s1 += g[c][j]; s2 += g[c][j] * xh[c][j];
+            acc_g[c][j] += a[j] * xh[c][j];
+            acc_b[c][j] += a[j];
+          }
+        }
+      }
+      const float m1 = warp_sum(s1) / float(d), m2 = warp_sum(s2) / float(d);
+#pragma unroll
+      for (int c = 0; c < CH; ++c) {
+        const int col = (c * 32 + lane) * 8;
+        if (col < d) {
+          float o[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = rstd[r] * (g[c][j] - m1 - xh[c][j] * m2);
+          *reinterpret_cast<uint4*>(dz + base + col) = pack8(o);
+          if (drop.thresh) {  // gradient seen by the Dense whose (dropped-out) output was added to the residual
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = drop_keep(dstream, base + col + j, drop.thresh) ? o[j] * drop.scale : 0.f;
+            *reinterpret_cast<uint4*>(dzm + base + col) = pack8(o);
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc_c[c][j] += round_bf16(o[j]);
         }
       }
     }
-    __syncthreads();
   }
+  // block reduce: every warp parks its sums in shared memory, then all threads add the 8 copies in warp order
+  float* mine_s = red + size_t(warp) * 3 * d;
+#pragma unroll
+  for (int c = 0; c < CH; ++c) {
+    const int col = (c * 32 + lane) * 8;
+    if (col < d) {
+#pragma unroll
+      for (int j = 0; j < 8; j += 4) {
+        *reinterpret_cast<float4*>(mine_s + col + j) = make_float4(acc_g[c][j], acc_g[c][j + 1], acc_g[c][j + 2], acc_g[c][j + 3]);
+        *reinterpret_cast<float4*>(mine_s + d + col + j) = make_float4(acc_b[c][j], acc_b[c][j + 1], acc_b[c][j + 2], acc_b[c][j + 3]);
+        *reinterpret_cast<float4*>(mine_s + 2 * d + col + j) = make_float4(acc_c[c][j], acc_c[c][j + 1], acc_c[c][j + 2], acc_c[c][j + 3]);
+      }
+    }
+  }
+  __syncthreads();
   float* mine = partials + size_t(blockIdx.x) * 3 * d;
-  for (int i = threadIdx.x; i < 3 * d; i += blockDim.x) mine[i] = red[i];
+  for (int i = threadIdx.x * 4; i < 3 * d; i += blockDim.x * 4) {
+    float4 s = *reinterpret_cast<const float4*>(red + i);
+#pragma unroll
+    for (int w = 1; w < kLnWarps; ++w) {
+      const float4 t = *reinterpret_cast<const float4*>(red + size_t(w) * 3 * d + i);
+      s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+    }
+    *reinterpret_cast<float4*>(mine + i) = s;
+  }
 }
 
-// dst[c] = sum_p src[p * stride + c] for a batch of jobs; block = 32 columns x 8 slices of the partials.
+// dst[c] = sum_p src[p * stride + c] for a batch of jobs; block = 32 columns x 32 slices of the partials.
 struct ReduceJobTable {
   static constexpr int kMax = 96;
   const float* src[kMax]; float* dst[kMax];
   int nparts[kMax], cols[kMax], stride[kMax], first_block[kMax + 1];
   int njobs;
 };
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 reduce_partials_kernel(const __grid_constant__ ReduceJobTable t) {
-  __shared__ float red[8][33];
+  __shared__ float red[32][33];
   int j = 0;
   while (j + 1 < t.njobs && int(blockIdx.x) >= t.first_block[j + 1]) ++j;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -212,14 +232,14 @@ reduce_partials_kernel(const __grid_constant__ ReduceJobTable t) {
     const float* s = t.src[j] + col;
     const int n = t.nparts[j], st = t.stride[j];
 #pragma unroll 4
-    for (int p = ty; p < n; p += 8) acc += __ldcg(s + size_t(p) * st);
+    for (int p = ty; p < n; p += 32) acc += __ldcg(s + size_t(p) * st);
   }
   red[ty][tx] = acc;
   __syncthreads();
   if (ty == 0 && col < t.cols[j]) {
     float v = red[0][tx];
 #pragma unroll
-    for (int i = 1; i < 8; ++i) v += red[i][tx];
+    for (int i = 1; i < 32; ++i) v += red[i][tx];
     t.dst[j][col] = v;
   }
 }
@@ -240,20 +260,36 @@ int layernorm_fwd(const bf16* x, const bf16* resid, const float* gamma, const fl
   return 0;
 }
 
-int ln_bwd_parts(int rows) { return std::max(1, std::min((rows + kLnWarps - 1) / kLnWarps, 2 * num_sms())); }
-size_t ln_bwd_scratch_floats(int rows, int d) { return size_t(ln_bwd_parts(rows)) * 3 * d; }
+namespace {
+int ln_rows_per_warp(int d) { return d <= 512 ? 2 : 1; }  // keeps the rows-in-flight register budget bounded
+}
+int ln_bwd_parts(int rows, int d) { const int per_block = kLnWarps * ln_rows_per_warp(d); return (rows + per_block - 1) / per_block; }
+size_t ln_bwd_scratch_floats(int rows, int d) { return size_t(ln_bwd_parts(rows, d)) * 3 * d; }
 
 int layernorm_bwd_partial(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const float* gamma, bf16* dz, int rows,
                           int d, float* partials, cudaStream_t stream, bf16* dzm, DropArgs drop) {
   if (drop.thresh && !dzm) return set_error("layernorm_bwd: dropout needs a dzm buffer");
   if (d % 8 || d > 2048) return set_error("layernorm: d=%d must be a multiple of 8 and <= 2048", d);
   if (rows <= 0) return set_error("layernorm_bwd: no rows");
-  const int grid = ln_bwd_parts(rows);
+  const int grid = ln_bwd_parts(rows, d);
   const int ch = (d + 255) / 256;
-  const size_t smem = size_t(3) * d * sizeof(float);
-#define LN_BWD(CH) ln_bwd_kernel<CH><<<grid, kLnWarps * 32, smem, stream>>>(dy, z, mean, rstd, gamma, dz, rows, d, partials, dzm, drop)
-  if (ch <= 1) LN_BWD(1); else if (ch <= 2) LN_BWD(2); else if (ch <= 4) LN_BWD(4); else LN_BWD(8);
-#undef LN_BWD
+  const size_t smem = size_t(kLnWarps) * 3 * d * sizeof(float);
+  auto launch = [&](auto kern) -> int {
+    if (smem > 48 * 1024) {
+      static std::mutex mu; static std::set<const void*> done;
+      std::lock_guard<std::mutex> lock(mu);
+      if (!done.count(reinterpret_cast<const void*>(kern))) {
+        B200XF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kLnWarps * 3 * 2048 * sizeof(float))));
+        done.insert(reinterpret_cast<const void*>(kern));
+      }
+    }
+    kern<<<grid, kLnWarps * 32, smem, stream>>>(dy, z, mean, rstd, gamma, dz, rows, d, partials, dzm, drop);
+    return 0;
+  };
+  if (ch <= 1) B200XF_TRY(launch(ln_bwd_kernel<1, 2>));
+  else if (ch <= 2) B200XF_TRY(launch(ln_bwd_kernel<2, 2>));
+  else if (ch <= 4) B200XF_TRY(launch(ln_bwd_kernel<4, 1>));
+  else B200XF_TRY(launch(ln_bwd_kernel<8, 1>));
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;
@@ -272,7 +308,7 @@ int reduce_partials(const ReduceJob* jobs, int njobs, cudaStream_t stream) {
     }
     t.first_block[t.njobs] = blocks;
     if (blocks == 0) continue;
-    reduce_partials_kernel<<<blocks, 256, 0, stream>>>(t);
+    reduce_partials_kernel<<<blocks, 1024, 0, stream>>>(t);
     B200XF_CUDA(cudaGetLastError());
     count_launch();
   }
@@ -283,7 +319,7 @@ int layernorm_bwd(const bf16* dy, const bf16* z, const float* mean, const float*
                   float* dgamma, float* dbeta, float* dcol, int rows, int d, float* scratch, cudaStream_t stream) {
   if (rows <= 0) return 0;
   B200XF_TRY(layernorm_bwd_partial(dy, z, mean, rstd, gamma, dz, rows, d, scratch, stream));
-  const int n = ln_bwd_parts(rows);
+  const int n = ln_bwd_parts(rows, d);
   ReduceJob jobs[3] = {{scratch, dgamma, n, d, 3 * d}, {scratch + d, dbeta, n, d, 3 * d}, {scratch + 2 * d, dcol, n, d, 3 * d}};
   return reduce_partials(jobs, dcol ? 3 : 2, stream);
 }
@@ -735,7 +771,8 @@ int cast_bf16_to_f32_2d(const bf16* in, int ldi, float* out, int ldo, int rows, 
 // variant below keeps the partials in a fixed array that is part of the loaded library image.
 namespace b200xf {
 namespace {
-// Capacity: 2 blocks per SM on a 148-SM part (296 blocks) x 3 sums x d <= 1024 columns = 909 312 floats (3.47 MiB).
+// Capacity: 909 312 floats (3.47 MiB) of per-block partial sums — one [3][d] partial per 16 rows (d <= 512) or per
+// 8 rows (larger d), i.e. up to 9 472 rows at d = 512 or 2 368 rows at d = 1024.
 // Every GPU that loads the library carries this array until the process exits.
 constexpr size_t kStaticLnScratchFloats = size_t(296) * 3 * 1024;
 static __device__ __align__(256) float g_ln_bwd_static_scratch[kStaticLnScratchFloats];
@@ -763,8 +800,8 @@ int static_ln_scratch(float** out) {
 
 // Same results as b200xf_layernorm_residual_bwd (same kernels, same summation order), no scratch argument and no
 // allocation of any kind: no cudaMalloc / cudaFree, no allocating library call.
-//  * Limit: b200xf_layernorm_bwd_scratch_bytes(rows, d) must not exceed 3 637 248 bytes (909 312 floats); that covers every
-//    row count for d <= 1024.  Larger problems are refused with an error, nothing is launched.
+//  * Limit: b200xf_layernorm_bwd_scratch_bytes(rows, d) must not exceed 3 637 248 bytes (909 312 floats): up to 9 472 rows
+//    at d = 512, 2 368 rows at d = 1024.  Larger problems are refused with an error, nothing is launched.
 //  * The first call on each device looks the array's address up (cudaGetSymbolAddress) with that device current; make that
 //    first call outside any stream capture.  `stream` must belong to the current device.
 //  * All calls on a device share the one array and it keeps whatever the previous call left in it.  Nothing in it has to be

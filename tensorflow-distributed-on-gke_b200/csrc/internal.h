@@ -78,8 +78,8 @@ int layernorm_fwd(const bf16* x, const bf16* resid, const float* gamma, const fl
 // fixed order: deterministic, and the many small reductions of a backward pass share one launch.
 struct ReduceJob { const float* src; float* dst; int nparts; int cols; int stride; };  // dst[c] = sum_p src[p*stride + c]
 int reduce_partials(const ReduceJob* jobs, int njobs, cudaStream_t stream);
-// dz = LN'(dy); partials [ln_bwd_parts(rows)][3][d] = per-block sums of (dy*xhat, dy, dz) -> dgamma, dbeta, colsum(dz).
-int ln_bwd_parts(int rows);
+// dz = LN'(dy); partials [ln_bwd_parts(rows, d)][3][d] = per-block sums of (dy*xhat, dy, dz) -> dgamma, dbeta, colsum(dz).
+int ln_bwd_parts(int rows, int d);
 size_t ln_bwd_scratch_floats(int rows, int d);
 // dzm (optional, with drop.thresh != 0): dz * dropout mask of the sub-layer output that was added to the residual — the
 // gradient the producing Dense sees; the third partial sum is then taken over dzm.

@@ -49,7 +49,7 @@ def test_noalloc_layernorm_bwd_matches_scratch_variant_twice_in_a_row():
 
 
 def test_noalloc_layernorm_bwd_rejects_sizes_beyond_its_buffer():
-    rows, d = 4096, 2048  # 296 blocks x 3 x 2048 floats = 7.3 MB > the 3.6 MB built-in array
+    rows, d = 4096, 2048  # 512 blocks x 3 x 2048 floats = 12.6 MB > the 3.6 MB built-in array
     t = torch.zeros(rows, d, device=DEV, dtype=torch.bfloat16)
     v = torch.zeros(rows, device=DEV); gm = torch.ones(d, device=DEV)
     rc, _ = _noalloc_bwd(t, t, v, v, gm)
