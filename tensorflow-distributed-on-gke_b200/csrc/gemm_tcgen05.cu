@@ -489,6 +489,11 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   }
 }
 
+int tensor_map_2d(const void* ptr, unsigned long long inner, unsigned long long outer, unsigned long long ld, unsigned box_outer,
+                  void* out_cu_tensor_map, int kind) {
+  return get_tmap(ptr, inner, outer, ld, box_outer, static_cast<CUtensorMap*>(out_cu_tensor_map), kind);
+}
+
 void gemm_set_trace(unsigned long long* dev_ptr) { g_gemm_trace = dev_ptr; }
 
 void gemm_clear_tensor_map_cache() {

@@ -48,6 +48,10 @@ struct GemmArgs {
 };
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream);
 void gemm_clear_tensor_map_cache();
+// Cached 2-D TMA descriptor (128B swizzle) of a row-major matrix: kind 0 = bf16 with a 64-column box, 1 = fp32 with a
+// 32-column box; `out_cu_tensor_map` points at a CUtensorMap.
+int tensor_map_2d(const void* ptr, unsigned long long inner, unsigned long long outer, unsigned long long ld, unsigned box_outer,
+                  void* out_cu_tensor_map, int kind);
 void gemm_set_trace(unsigned long long* dev_ptr);  // debug: per-CTA phase time stamps (8 x u64 per CTA), null to disable
 
 // ---- attention (fused, masks derived in-tile from token ids; transformer_model.py:73-109,350-363)
@@ -70,6 +74,9 @@ struct AttnArgs {
 };
 int attention_fwd(const AttnArgs& a, cudaStream_t stream);
 int attention_bwd(const AttnArgs& a, cudaStream_t stream);
+// tcgen05 single-tile path (Sq, Sk <= 128, head size 64); B200XF_ATTENTION_TC=0 disables it
+bool attention_tc_supported(const AttnArgs& a);
+int attention_bwd_tc(const AttnArgs& a, cudaStream_t stream);
 
 // ---- LayerNorm (+ optional residual add) fwd / bwd (transformer_model.py:187-188,198,204)
 int layernorm_fwd(const bf16* x, const bf16* resid, const float* gamma, const float* beta, bf16* y, bf16* z_out,

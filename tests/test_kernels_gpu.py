@@ -108,6 +108,9 @@ ATTN_CASES = [  # B, H, Sq, Sk, dk, causal, pad_first_token
     (2, 8, 40, 40, 16, False, False), (2, 8, 40, 40, 16, True, False), (3, 4, 40, 33, 32, False, False),
     (2, 8, 128, 128, 64, True, False), (2, 8, 128, 128, 64, False, False), (1, 2, 200, 77, 64, False, False),
     (2, 2, 70, 70, 16, True, True), (1, 2, 300, 300, 64, True, False),
+    # single-tile tcgen05 backward (Sq, Sk <= 128, dk 64): ragged tile, cross shapes, fully masked causal rows
+    (3, 4, 100, 100, 64, True, False), (2, 8, 128, 77, 64, False, False), (2, 4, 40, 128, 64, False, False),
+    (2, 2, 128, 128, 64, True, True), (5, 3, 17, 9, 64, False, False),
 ]
 
 
