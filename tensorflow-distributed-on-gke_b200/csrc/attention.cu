@@ -143,6 +143,8 @@ struct FwdSmem { typename Smem<DK>::Tile q, k[2], v[2]; int mask[2][kTile]; };
 template <int DK>
 __global__ void __launch_bounds__(kWarps * 32)
 attn_fwd_kernel(const KernelArgs p) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ __align__(16) uint8_t smem_raw[];
   FwdSmem<DK>& sm = *reinterpret_cast<FwdSmem<DK>*>(smem_raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
@@ -254,6 +256,8 @@ struct DqSmem { typename Smem<DK>::Tile q, d_o, k[2], v[2]; int mask[2][kTile]; 
 template <int DK>
 __global__ void __launch_bounds__(kWarps * 32)
 attn_bwd_dq_kernel(const KernelArgs p) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ __align__(16) uint8_t smem_raw[];
   DqSmem<DK>& sm = *reinterpret_cast<DqSmem<DK>*>(smem_raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
@@ -356,6 +360,8 @@ struct DkvSmem { typename Smem<DK>::Tile k, v, q[2], d_o[2]; float lse_m[2][kTil
 template <int DK>
 __global__ void __launch_bounds__(kWarps * 32)
 attn_bwd_dkv_kernel(const KernelArgs p) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ __align__(16) uint8_t smem_raw[];
   DkvSmem<DK>& sm = *reinterpret_cast<DkvSmem<DK>*>(smem_raw);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t4 = lane & 3;
@@ -470,8 +476,7 @@ int launch_attn(Kern kern, size_t smem, dim3 grid, const KernelArgs& p, cudaStre
       configured.insert(reinterpret_cast<const void*>(kern));
     }
   }
-  kern<<<grid, kWarps * 32, smem, stream>>>(p);
-  B200XF_CUDA(cudaGetLastError());
+  B200XF_CUDA(launch_k(kern, grid, kWarps * 32, smem, stream, p));
   count_launch();
   return 0;
 }

@@ -79,6 +79,8 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     ptx::fence_barrier_init();
   }
   if (warp == 1) { ptx::tmem_alloc(tmem_slot, 512); ptx::tmem_relinquish(); }
+  pdl_wait();   // everything above overlaps the tail of the previous kernel
+  pdl_trigger();
   if (warp >= 2) {
     const int j = threadIdx.x - 64;
     s_mask[j] = (j >= p.Sk) ? 2 : (p.key_tokens[size_t(b) * p.Sk + j] == 0 ? 1 : 0);
@@ -233,8 +235,7 @@ int attention_bwd_tc(const AttnArgs& a, cudaStream_t stream) {
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] { attr_err = cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBwd); });
   if (attr_err != cudaSuccess) return set_error("cudaFuncSetAttribute(attn_bwd_tc): %s", cudaGetErrorString(attr_err));
-  attn_bwd_tc_kernel<<<dim3(a.H, a.B), kThreads, kSmemBwd, stream>>>(tq, tk, tv, tdo, p);
-  B200XF_CUDA(cudaGetLastError());
+  B200XF_CUDA(launch_k(attn_bwd_tc_kernel, dim3(a.H, a.B), kThreads, kSmemBwd, stream, tq, tk, tv, tdo, p));
   count_launch();
   return 0;
 }

@@ -41,6 +41,8 @@ __global__ void __launch_bounds__(kLnWarps * 32)
 ln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ resid, const float* __restrict__ gamma,
               const float* __restrict__ beta, bf16* __restrict__ y, bf16* __restrict__ z_out, float* __restrict__ mean_out,
               float* __restrict__ rstd_out, int rows, int d, float eps) {
+  pdl_wait();
+  pdl_trigger();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * kLnWarps + warp;
   if (row >= rows) return;
@@ -105,6 +107,8 @@ __global__ void __launch_bounds__(kLnWarps * 32, (CH * RPW <= 4) ? 2 : 1)
 ln_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, const float* __restrict__ mean_in,
               const float* __restrict__ rstd_in, const float* __restrict__ gamma, bf16* __restrict__ dz, int rows, int d,
               float* __restrict__ partials, bf16* __restrict__ dzm, const DropArgs drop) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ float red[];  // [kLnWarps][3][d]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row0 = (blockIdx.x * kLnWarps + warp) * RPW;
@@ -222,6 +226,8 @@ struct ReduceJobTable {
 };
 __global__ void __launch_bounds__(1024)
 reduce_partials_kernel(const __grid_constant__ ReduceJobTable t) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float red[32][33];
   int j = 0;
   while (j + 1 < t.njobs && int(blockIdx.x) >= t.first_block[j + 1]) ++j;
@@ -252,7 +258,7 @@ int layernorm_fwd(const bf16* x, const bf16* resid, const float* gamma, const fl
   if (rows <= 0) return 0;
   const int grid = (rows + kLnWarps - 1) / kLnWarps;
   const int ch = (d + 255) / 256;
-#define LN_FWD(CH) ln_fwd_kernel<CH><<<grid, kLnWarps * 32, 0, stream>>>(x, resid, gamma, beta, y, z_out, mean, rstd, rows, d, eps)
+#define LN_FWD(CH) B200XF_CUDA(launch_k(ln_fwd_kernel<CH>, grid, kLnWarps * 32, 0, stream, x, resid, gamma, beta, y, z_out, mean, rstd, rows, d, eps))
   if (ch <= 1) LN_FWD(1); else if (ch <= 2) LN_FWD(2); else if (ch <= 4) LN_FWD(4); else LN_FWD(8);
 #undef LN_FWD
   B200XF_CUDA(cudaGetLastError());
@@ -283,7 +289,7 @@ int layernorm_bwd_partial(const bf16* dy, const bf16* z, const float* mean, cons
         done.insert(reinterpret_cast<const void*>(kern));
       }
     }
-    kern<<<grid, kLnWarps * 32, smem, stream>>>(dy, z, mean, rstd, gamma, dz, rows, d, partials, dzm, drop);
+    B200XF_CUDA(launch_k(kern, grid, kLnWarps * 32, smem, stream, dy, z, mean, rstd, gamma, dz, rows, d, partials, dzm, drop));
     return 0;
   };
   if (ch <= 1) B200XF_TRY(launch(ln_bwd_kernel<1, 2>));
@@ -308,7 +314,7 @@ int reduce_partials(const ReduceJob* jobs, int njobs, cudaStream_t stream) {
     }
     t.first_block[t.njobs] = blocks;
     if (blocks == 0) continue;
-    reduce_partials_kernel<<<blocks, 1024, 0, stream>>>(t);
+    B200XF_CUDA(launch_k(reduce_partials_kernel, blocks, 1024, 0, stream, t));
     B200XF_CUDA(cudaGetLastError());
     count_launch();
   }
@@ -330,6 +336,8 @@ namespace {
 // x[b,s,:] = table[token] * sqrt(d) + pe[s]   (fp32 master rows gathered bit-exactly, output bf16)
 __global__ void embed_fwd_kernel(const long long* __restrict__ tokens, const float* __restrict__ table, int vocab,
                                  const float* __restrict__ pe, bf16* __restrict__ out, int S, int d, float scale, const DropArgs drop) {
+  pdl_wait();
+  pdl_trigger();
   const int n = blockIdx.x;
   const unsigned long long dstream = drop.thresh ? drop_stream(drop) : 0ull;
   const long long tok = tokens[n];
@@ -354,6 +362,8 @@ __global__ void embed_fwd_kernel(const long long* __restrict__ tokens, const flo
 }
 
 __global__ void embed_keys_kernel(const long long* __restrict__ tokens, int* __restrict__ keys, int* __restrict__ vals, int n, int vocab) {
+  pdl_wait();
+  pdl_trigger();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const long long t = tokens[i];
@@ -365,6 +375,8 @@ __global__ void embed_keys_kernel(const long long* __restrict__ tokens, int* __r
 // gradient rows in sorted (= original position) order and writes the table row once: deterministic.
 __global__ void embed_bwd_kernel(const int* __restrict__ keys, const int* __restrict__ vals, const bf16* __restrict__ dx,
                                  float* __restrict__ dtable, int n, int d, int vocab, float scale, const DropArgs drop) {
+  pdl_wait();
+  pdl_trigger();
   const int p = blockIdx.x;
   const unsigned long long dstream = drop.thresh ? drop_stream(drop) : 0ull;
   const int key = keys[p];
@@ -400,7 +412,7 @@ int embed_pe_fwd(const long long* tokens, const float* table, int vocab, const f
   const int n = B * S;
   if (n <= 0) return 0;
   const int threads = min(256, max(32, (d / 4 + 31) / 32 * 32));
-  embed_fwd_kernel<<<n, threads, 0, stream>>>(tokens, table, vocab, pe, out, S, d, sqrtf(float(d)), drop);
+  B200XF_CUDA(launch_k(embed_fwd_kernel, n, threads, 0, stream, tokens, table, vocab, pe, out, S, d, sqrtf(float(d)), drop));
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;
@@ -424,12 +436,12 @@ int embed_bwd(const long long* tokens, const bf16* dx, float* dtable, int vocab,
   int* vals_out = reinterpret_cast<int*>(base + 3 * seg);
   void* temp = base + 4 * seg;
   size_t temp_bytes = scratch_bytes - 4 * seg;
-  embed_keys_kernel<<<(n + 255) / 256, 256, 0, stream>>>(tokens, keys_in, vals_in, n, vocab);
+  B200XF_CUDA(launch_k(embed_keys_kernel, (n + 255) / 256, 256, 0, stream, tokens, keys_in, vals_in, n, vocab));
   int bits = 1;
   while ((1ll << bits) <= vocab) ++bits;
   B200XF_CUDA(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, n, 0, bits, stream));
   const int threads = min(256, max(32, (d / 4 + 31) / 32 * 32));
-  embed_bwd_kernel<<<n, threads, 0, stream>>>(keys_out, vals_out, dx, dtable, n, d, vocab, sqrtf(float(d)), drop);
+  B200XF_CUDA(launch_k(embed_bwd_kernel, n, threads, 0, stream, keys_out, vals_out, dx, dtable, n, d, vocab, sqrtf(float(d)), drop));
   B200XF_CUDA(cudaGetLastError());
   count_launch(3);
   return 0;
@@ -456,6 +468,8 @@ int dropout_mask_fill(float* out, int rows, int cols, DropArgs drop, cudaStream_
 namespace {
 __global__ void prep_targets_kernel(const long long* __restrict__ target, long long* __restrict__ tgt_in,
                                     long long* __restrict__ labels, int* __restrict__ count, int B, int T1) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ int warp_cnt[32];
   const int T = T1 - 1;
   int local = 0;
@@ -479,7 +493,7 @@ __global__ void prep_targets_kernel(const long long* __restrict__ target, long l
 int prep_targets(const long long* target, long long* tgt_in, long long* labels, int* nonpad_count, int B, int T_plus_1,
                  cudaStream_t stream) {
   if (T_plus_1 < 2) return set_error("target must have at least 2 positions");
-  prep_targets_kernel<<<1, 1024, 0, stream>>>(target, tgt_in, labels, nonpad_count, B, T_plus_1);
+  B200XF_CUDA(launch_k(prep_targets_kernel, 1, 1024, 0, stream, target, tgt_in, labels, nonpad_count, B, T_plus_1));
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;
@@ -502,6 +516,8 @@ __global__ void __launch_bounds__(kCeThreads)
 vocab_ce_kernel(bf16* __restrict__ logits, int ldl, const long long* __restrict__ labels, int V,
                 const int* __restrict__ nonpad_count, float inv_workers, float* __restrict__ row_loss,
                 int* __restrict__ row_correct, int write_grad) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float sm_m[kCeThreads / 32], sm_s[kCeThreads / 32], sm_am[kCeThreads / 32];
   __shared__ int sm_ai[kCeThreads / 32];
   __shared__ float bc[3];
@@ -585,6 +601,8 @@ vocab_ce_kernel(bf16* __restrict__ logits, int ldl, const long long* __restrict_
 
 __global__ void ce_finalize_kernel(const float* __restrict__ row_loss, const int* __restrict__ row_correct,
                                    const int* __restrict__ nonpad_count, int rows, float inv_workers, float* __restrict__ out3) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float wl[32]; __shared__ int wc[32];
   float l = 0.f; int c = 0;
   // fixed assignment of rows to threads and a fixed reduction tree: deterministic
@@ -607,7 +625,7 @@ int vocab_ce_fwd_bwd(bf16* logits, int ldl, const long long* labels, int rows, i
                      float* row_loss, int* row_correct, int write_grad, cudaStream_t stream) {
   if (ldl % 8) return set_error("vocab_ce: ld=%d must be a multiple of 8", ldl);
   if (rows <= 0) return 0;
-  vocab_ce_kernel<<<rows, kCeThreads, 0, stream>>>(logits, ldl, labels, V, nonpad_count, inv_workers, row_loss, row_correct, write_grad);
+  B200XF_CUDA(launch_k(vocab_ce_kernel, rows, kCeThreads, 0, stream, logits, ldl, labels, V, nonpad_count, inv_workers, row_loss, row_correct, write_grad));
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;
@@ -615,7 +633,7 @@ int vocab_ce_fwd_bwd(bf16* logits, int ldl, const long long* labels, int rows, i
 
 int ce_finalize(const float* row_loss, const int* row_correct, const int* nonpad_count, int rows, float inv_workers, float* out3,
                 cudaStream_t stream) {
-  ce_finalize_kernel<<<1, 1024, 0, stream>>>(row_loss, row_correct, nonpad_count, rows, inv_workers, out3);
+  B200XF_CUDA(launch_k(ce_finalize_kernel, 1, 1024, 0, stream, row_loss, row_correct, nonpad_count, rows, inv_workers, out3));
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;
@@ -628,6 +646,8 @@ namespace {
 __global__ void __launch_bounds__(256)
 adam_kernel(float4* __restrict__ w, float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v,
             uint2* __restrict__ wb, size_t n4, const long long* __restrict__ iterations, AdamHyper h, int zero_grad) {
+  pdl_wait();
+  pdl_trigger();
   const float step = float(*iterations);
   const float lr = h.rsqrt_d_model * fminf(step * h.warmup_pow_m15, 1.0f / sqrtf(step));
   const float t = step + 1.0f;
@@ -648,7 +668,9 @@ adam_kernel(float4* __restrict__ w, float4* __restrict__ g, float4* __restrict__
     if (zero_grad) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
 }
-__global__ void increment_kernel(long long* c) { *c += 1; }
+__global__ void increment_kernel(long long* c) {
+  pdl_wait();
+  pdl_trigger(); *c += 1; }
 }  // namespace
 
 int adam_step(float* w, float* g, float* m, float* v, bf16* w_bf16, size_t n, const long long* iterations_dev, AdamHyper h,
@@ -657,15 +679,15 @@ int adam_step(float* w, float* g, float* m, float* v, bf16* w_bf16, size_t n, co
   if (n == 0) return 0;
   const size_t n4 = n / 4;
   const int grid = int(std::min<size_t>((n4 + 255) / 256, size_t(num_sms()) * 8));
-  adam_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<float4*>(w), reinterpret_cast<float4*>(g), reinterpret_cast<float4*>(m),
-                                        reinterpret_cast<float4*>(v), reinterpret_cast<uint2*>(w_bf16), n4, iterations_dev, h, zero_grad);
+  B200XF_CUDA(launch_k(adam_kernel, grid, 256, 0, stream, reinterpret_cast<float4*>(w), reinterpret_cast<float4*>(g), reinterpret_cast<float4*>(m),
+                       reinterpret_cast<float4*>(v), reinterpret_cast<uint2*>(w_bf16), n4, iterations_dev, h, zero_grad));
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;
 }
 
 int increment_counter(long long* iterations_dev, cudaStream_t stream) {
-  increment_kernel<<<1, 1, 0, stream>>>(iterations_dev);
+  B200XF_CUDA(launch_k(increment_kernel, 1, 1, 0, stream, iterations_dev));
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;
@@ -676,6 +698,8 @@ namespace {
 // partial[strip][c] = sum over the strip's rows of x[r][c]; block = 8 column groups (8 bf16 each) x 32 row phases.
 __global__ void __launch_bounds__(256)
 colsum_partial_kernel(const bf16* __restrict__ x, int ld, int rows, int cols, int rows_per_strip, float* __restrict__ partials) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float red[32][65];
   const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;
   const int col = blockIdx.x * 64 + tx * 8;
@@ -707,6 +731,8 @@ colsum_partial_kernel(const bf16* __restrict__ x, int ld, int rows, int cols, in
 }
 
 __global__ void cast_kernel(const float4* __restrict__ in, uint2* __restrict__ out, size_t n4) {
+  pdl_wait();
+  pdl_trigger();
   for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x) {
     const float4 f = in[i];
     uint2 u; u.x = ptx::pack_bf16x2(f.x, f.y); u.y = ptx::pack_bf16x2(f.z, f.w);
@@ -734,7 +760,7 @@ int colsum_partial(const bf16* x, int ld, int rows, int cols, float* partials, c
   if (cols <= 0 || rows <= 0) return set_error("colsum: empty problem");
   const int strips = colsum_parts(rows, cols);
   const int rps = (rows + strips - 1) / strips;
-  colsum_partial_kernel<<<dim3((cols + 63) / 64, strips), 256, 0, stream>>>(x, ld, rows, cols, rps, partials);
+  B200XF_CUDA(launch_k(colsum_partial_kernel, dim3((cols + 63) / 64, strips), 256, 0, stream, x, ld, rows, cols, rps, partials));
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;
@@ -745,7 +771,7 @@ int cast_f32_to_bf16(const float* in, bf16* out, size_t n, cudaStream_t stream) 
   if (n == 0) return 0;
   const size_t n4 = n / 4;
   const int grid = int(std::min<size_t>((n4 + 255) / 256, size_t(num_sms()) * 8));
-  cast_kernel<<<grid, 256, 0, stream>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<uint2*>(out), n4);
+  B200XF_CUDA(launch_k(cast_kernel, grid, 256, 0, stream, reinterpret_cast<const float4*>(in), reinterpret_cast<uint2*>(out), n4));
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;

@@ -145,6 +145,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();     // barrier init, TMEM allocation and descriptor prefetch above overlap the previous kernel's tail
+  pdl_trigger();
   if (threadIdx.x == 0) stamp(p, 1);
 
   const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
@@ -399,8 +401,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, 
     if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gemm): %s", cudaGetErrorString(e));
     attr_set = true;
   }
-  kern<<<grid, kThreads, Cfg<BN>::kSmem, stream>>>(ta, tb, td, p);
-  cudaError_t e = cudaGetLastError();
+  cudaError_t e = launch_k(kern, grid, kThreads, Cfg<BN>::kSmem, stream, ta, tb, td, p);
   if (e != cudaSuccess) return set_error("gemm launch: %s", cudaGetErrorString(e));
   count_launch();
   return 0;

@@ -19,6 +19,20 @@ int num_sms();
 void count_launch(int n = 1);
 long long launches_total();
 
+bool pdl_enabled();  // B200XF_PDL=0 switches programmatic dependent launch off
+
+// Launch with the programmatic-stream-serialization attribute (see ptx.cuh: pdl_wait / pdl_trigger).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 #define B200XF_CUDA(expr)                                                                          \
   do {                                                                                             \
     cudaError_t _e = (expr);                                                                       \

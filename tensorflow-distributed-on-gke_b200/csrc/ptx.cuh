@@ -139,6 +139,14 @@ __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v 
 
 }  // namespace ptx
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// Kernels are launched with programmatic stream serialization: a kernel may be scheduled while its predecessor is still
+// draining.  pdl_wait() blocks until the predecessor grid has completed and its writes are visible (a no-op for a normal
+// launch); pdl_trigger() lets the successor start being scheduled.  Every kernel calls pdl_wait() before it touches
+// global memory, so completion stays transitive along the stream.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---------------------------------------------------------------- dropout (counter-based, recomputed in backward)
 // keep(element) = hash(key, element index) >= rate * 2^32, key = f(seed, site, optimizer step): no mask is stored.
 struct DropArgs {
