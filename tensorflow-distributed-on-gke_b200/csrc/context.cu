@@ -259,8 +259,8 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   for (int l = 0; l < L; ++l) { need(3 * nd, 2); for (int i = 0; i < 8; ++i) need(nd, 2); need(nff, 2); need(4 * N * H, 4); need(6 * N, 4); }
   need(N * size_t(L) * 2 * d, 2); need(N * size_t(L) * 2 * d, 2);   // kv_all, dkv_all
   need(N * size_t(vt_ld), 2);                                       // logits / dlogits
-  for (int i = 0; i < 6; ++i) need(nd, 2);                          // dA dB dz dzm dctx dq2
-  need(nff, 2); need(3 * nd, 2);                                    // dh dqkv
+  for (int i = 0; i < 9; ++i) need(nd, 2);                          // dA dB dctx, 2 x (dz dzm dq2)
+  need(2 * nff, 2); need(2 * 3 * nd, 2);                            // 2 x dh, 2 x dqkv
   need(N * H, 4);                                                   // delta
   for (int i = 0; i < 4; ++i) need(N + 64, 8);                      // inp, target, tgt_in, labels
   need(N, 4); need(N, 4);                                           // row_loss, row_correct
@@ -292,9 +292,13 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   }
   B200XF_TRY(arena_alloc(&kv, N * size_t(L) * 2 * d)); B200XF_TRY(arena_alloc(&dkv, N * size_t(L) * 2 * d));
   B200XF_TRY(arena_alloc(&logits, N * size_t(vt_ld)));
-  B200XF_TRY(arena_alloc(&dA, nd)); B200XF_TRY(arena_alloc(&dB, nd)); B200XF_TRY(arena_alloc(&dz, nd));
-  B200XF_TRY(arena_alloc(&dctx, nd)); B200XF_TRY(arena_alloc(&dq2, nd)); B200XF_TRY(arena_alloc(&dzm, nd));
-  B200XF_TRY(arena_alloc(&dh, nff)); B200XF_TRY(arena_alloc(&dqkv, 3 * nd));
+  B200XF_TRY(arena_alloc(&dA, nd)); B200XF_TRY(arena_alloc(&dB, nd)); B200XF_TRY(arena_alloc(&dctx, nd));
+  for (int c = 0; c < 2; ++c) {
+    B200XF_TRY(arena_alloc(&sb_dz.buf[c], nd)); B200XF_TRY(arena_alloc(&sb_dzm.buf[c], nd)); B200XF_TRY(arena_alloc(&sb_dq2.buf[c], nd));
+    B200XF_TRY(arena_alloc(&sb_dh.buf[c], nff)); B200XF_TRY(arena_alloc(&sb_dqkv.buf[c], 3 * nd));
+    for (SideBuf* b : {&sb_dz, &sb_dzm, &sb_dq2, &sb_dh, &sb_dqkv}) B200XF_CUDA(cudaEventCreateWithFlags(&b->done[c], cudaEventDisableTiming));
+  }
+  dz = sb_dz.buf[0]; dzm = sb_dzm.buf[0]; dq2 = sb_dq2.buf[0]; dh = sb_dh.buf[0]; dqkv = sb_dqkv.buf[0];
   B200XF_TRY(arena_alloc(&delta, N * H));
   B200XF_TRY(arena_alloc(&tok_inp, N + 64)); B200XF_TRY(arena_alloc(&tok_target, N + 64));
   B200XF_TRY(arena_alloc(&tok_tgt_in, N + 64)); B200XF_TRY(arena_alloc(&tok_labels, N + 64));
@@ -324,6 +328,10 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   adam.warmup_pow_m15 = float(pow(double(hp.warmup_steps), -1.5));
   B200XF_CUDA(cudaMallocHost(&host_out, 64));
   B200XF_CUDA(cudaStreamCreateWithFlags(&comm_stream, cudaStreamNonBlocking));
+  B200XF_CUDA(cudaStreamCreateWithFlags(&side_stream, cudaStreamNonBlocking));
+  B200XF_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+  B200XF_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+  if (const char* e = getenv("B200XF_SIDE_WGRAD")) side_on = atoi(e) != 0;
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_ready, cudaEventDisableTiming));
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_done, cudaEventDisableTiming));
   return 0;
@@ -336,6 +344,10 @@ Context::~Context() {
   cudaFree(params); cudaFree(grads); cudaFree(adam_m); cudaFree(adam_v); cudaFree(shadow); cudaFree(arena);
   if (host_out) cudaFreeHost(host_out);
   if (comm_stream) cudaStreamDestroy(comm_stream);
+  if (side_stream) { cudaStreamSynchronize(side_stream); cudaStreamDestroy(side_stream); }
+  if (ev_fork) cudaEventDestroy(ev_fork);
+  if (ev_join) cudaEventDestroy(ev_join);
+  for (SideBuf* b : {&sb_dz, &sb_dzm, &sb_dq2, &sb_dh, &sb_dqkv}) for (int c = 0; c < 2; ++c) if (b->done[c]) cudaEventDestroy(b->done[c]);
   if (ev_ready) cudaEventDestroy(ev_ready);
   if (ev_done) cudaEventDestroy(ev_done);
   gemm_clear_tensor_map_cache();
@@ -398,6 +410,36 @@ DropArgs Context::site_drop(int site) const {
   return d;
 }
 
+// ------------------------------------------------------------------------------------ side stream (wgrad, bias sums)
+int Context::sb_write(SideBuf& b, bf16** out) {
+  b.cur ^= 1;
+  if (b.pending[b.cur]) { B200XF_CUDA(cudaStreamWaitEvent(stream, b.done[b.cur], 0)); b.pending[b.cur] = false; }
+  *out = b.buf[b.cur];
+  return 0;
+}
+int Context::side_launch_begin(cudaStream_t* s) {
+  if (!side_on) { *s = stream; return 0; }
+  B200XF_CUDA(cudaEventRecord(ev_fork, stream));               // everything the compute stream has produced so far ...
+  B200XF_CUDA(cudaStreamWaitEvent(side_stream, ev_fork, 0));   // ... is visible to the side stream
+  side_dirty = true;
+  *s = side_stream;
+  return 0;
+}
+int Context::side_launch_end(const void* read_ptr) {
+  if (!side_on) return 0;
+  for (SideBuf* b : {&sb_dz, &sb_dzm, &sb_dq2, &sb_dh, &sb_dqkv})
+    for (int c = 0; c < 2; ++c)
+      if (read_ptr == b->buf[c]) { B200XF_CUDA(cudaEventRecord(b->done[c], side_stream)); b->pending[c] = true; }
+  return 0;
+}
+int Context::join_side() {
+  if (!side_on || !side_dirty) return 0;
+  B200XF_CUDA(cudaEventRecord(ev_join, side_stream));
+  B200XF_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
+  side_dirty = false;
+  return 0;
+}
+
 // ------------------------------------------------------------------------------------ GEMM helpers
 int Context::dense_fwd(const bf16* x, int M, const Dense& p, bf16* y, int relu, const bf16* resid, int drop_site) {
   GemmArgs g;
@@ -425,7 +467,10 @@ int Context::dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p) {
   g.b = dy; g.ldb = p.ld; g.b_mn = 1;  // dY [tokens][N] == B stored [contract][N]
   g.d = grads + p.w; g.ldd = p.ld; g.d_fp32 = 1; g.accumulate = 1;
   g.M = p.K; g.N = p.N; g.K = M;
-  return gemm_bf16(g, stream);
+  cudaStream_t s;
+  B200XF_TRY(side_launch_begin(&s));
+  B200XF_TRY(gemm_bf16(g, s));
+  return side_launch_end(dy);
 }
 
 // ------------------------------------------------------------------------------------ forward
@@ -523,6 +568,8 @@ int Context::ln_bwd(const bf16* dy, const bf16* z, const float* st_mean, const f
   float* part = red_alloc(size_t(n) * 3 * d);
   if (!part) return set_error("reduction scratch exhausted");
   const DropArgs drop = site_drop(drop_site);
+  B200XF_TRY(sb_write(sb_dz, &dz));
+  if (drop.thresh) B200XF_TRY(sb_write(sb_dzm, &dzm));
   dsub = drop.thresh ? dzm : dz;  // what the Dense that fed this residual sees
   B200XF_TRY(layernorm_bwd_partial(dy, z, st_mean, st_rstd, params + p.g, dz, rows, d, part, stream, dzm, drop));
   red_jobs.push_back({part, grads + p.g, n, d, 3 * d});
@@ -535,9 +582,11 @@ int Context::colsum(const bf16* x, int ld, int rows, int cols, size_t dst_off) {
   const int n = colsum_parts(rows, cols);
   float* part = red_alloc(size_t(n) * cols);
   if (!part) return set_error("reduction scratch exhausted");
-  B200XF_TRY(colsum_partial(x, ld, rows, cols, part, stream));
+  cudaStream_t s;
+  B200XF_TRY(side_launch_begin(&s));
+  B200XF_TRY(colsum_partial(x, ld, rows, cols, part, s));
   red_jobs.push_back({part, grads + dst_off, n, cols, cols});
-  return 0;
+  return side_launch_end(x);
 }
 
 // One launch sums every pending set of column-sum partials (bias / gamma / beta gradients) into the flat gradient.
@@ -572,6 +621,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     // LN3 / FFN
     B200XF_TRY(ln_bwd(cur, a.z3, st + 4 * Nt, st + 5 * Nt, w.ln3, w.f2.b, Nt, 4 + 2 * L + 3 * l));
     B200XF_TRY(dense_wgrad(a.h, dsub, Nt, w.f2));
+    B200XF_TRY(sb_write(sb_dh, &dh));
     B200XF_TRY(dense_dgrad(dsub, Nt, w.f2, dh, a.h, 2));
     B200XF_TRY(colsum(dh, w.f1.ld, Nt, w.f1.N, w.f1.b));
     B200XF_TRY(dense_wgrad(a.o2, dh, Nt, w.f1));
@@ -585,6 +635,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     c2.q = a.q2; c2.ldq = d; c2.k = kv + size_t(l) * 2 * d; c2.v = kv + size_t(l) * 2 * d + d; c2.ldk = c2.ldv = kv_all.ld;
     c2.o = a.ctx2; c2.ldo = d; c2.lse = a.lse2; c2.key_tokens = inp; c2.causal = 0;
     c2.B = B; c2.H = H; c2.Sq = T; c2.Sk = S; c2.dk = dk;
+    B200XF_TRY(sb_write(sb_dq2, &dq2));
     c2.d_o = dctx; c2.lddo = d; c2.dq = dq2; c2.lddq = d;
     c2.dk_out = dkv + size_t(l) * 2 * d; c2.dv_out = dkv + size_t(l) * 2 * d + d; c2.lddk = c2.lddv = kv_all.ld; c2.delta = delta;
     B200XF_TRY(attention_bwd(c2, stream));
@@ -600,6 +651,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     s1.q = a.qkv; s1.k = a.qkv + d; s1.v = a.qkv + 2 * d; s1.ldq = s1.ldk = s1.ldv = 3 * d;
     s1.o = a.ctx1; s1.ldo = d; s1.lse = a.lse1; s1.key_tokens = tgt_in; s1.causal = 1;
     s1.B = B; s1.H = H; s1.Sq = T; s1.Sk = T; s1.dk = dk;
+    B200XF_TRY(sb_write(sb_dqkv, &dqkv));
     s1.d_o = dctx; s1.lddo = d; s1.dq = dqkv; s1.dk_out = dqkv + d; s1.dv_out = dqkv + 2 * d; s1.lddq = s1.lddk = s1.lddv = 3 * d;
     s1.delta = delta;
     B200XF_TRY(attention_bwd(s1, stream));
@@ -622,6 +674,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     float* st = a.stats;
     B200XF_TRY(ln_bwd(cur, a.z2, st + 2 * Ns, st + 3 * Ns, w.ln2, w.f2.b, Ns, 3 + 2 * l));
     B200XF_TRY(dense_wgrad(a.h, dsub, Ns, w.f2));
+    B200XF_TRY(sb_write(sb_dh, &dh));
     B200XF_TRY(dense_dgrad(dsub, Ns, w.f2, dh, a.h, 2));
     B200XF_TRY(colsum(dh, w.f1.ld, Ns, w.f1.N, w.f1.b));
     B200XF_TRY(dense_wgrad(a.o1, dh, Ns, w.f1));
@@ -634,6 +687,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     at.q = a.qkv; at.k = a.qkv + d; at.v = a.qkv + 2 * d; at.ldq = at.ldk = at.ldv = 3 * d;
     at.o = a.ctx; at.ldo = d; at.lse = a.lse; at.key_tokens = inp; at.causal = 0;
     at.B = B; at.H = H; at.Sq = S; at.Sk = S; at.dk = dk;
+    B200XF_TRY(sb_write(sb_dqkv, &dqkv));
     at.d_o = dctx; at.lddo = d; at.dq = dqkv; at.dk_out = dqkv + d; at.dv_out = dqkv + 2 * d; at.lddq = at.lddk = at.lddv = 3 * d;
     at.delta = delta;
     B200XF_TRY(attention_bwd(at, stream));
@@ -645,6 +699,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
   }
   B200XF_TRY(embed_bwd(inp, cur, grads + enc_emb, hp.input_vocabulary_size, Ns, d, emb_scratch, emb_scratch_bytes, stream, site_drop(0)));
   B200XF_TRY(section_done());
+  B200XF_TRY(join_side());
   B200XF_TRY(flush_reductions());
   return 0;
 }
@@ -659,6 +714,7 @@ int Context::section_done() {
   const size_t end = sections[idx].second;
   const bool last = (idx + 1 == sections.size());
   if (!last && (end - bucket_begin) * sizeof(float) < bucket_bytes) return 0;
+  B200XF_TRY(join_side());
   B200XF_TRY(flush_reductions());
   B200XF_CUDA(cudaEventRecord(ev_ready, stream));
   B200XF_CUDA(cudaStreamWaitEvent(comm_stream, ev_ready, 0));

@@ -48,6 +48,18 @@ struct Context {
   char* arena = nullptr; size_t arena_size = 0, arena_used = 0;
   bf16 *enc_x = nullptr, *dec_x = nullptr, *kv = nullptr, *dkv = nullptr, *logits = nullptr;
   std::vector<EncAct> ea; std::vector<DecAct> da;
+  // Weight-gradient GEMMs and bias column sums run on a second stream, off the dgrad / LayerNorm / attention critical
+  // path.  Buffers they read are double buffered: before the compute stream rewrites a copy it waits for the side-stream
+  // readers of that copy (normally long finished).
+  struct SideBuf { bf16* buf[2] = {nullptr, nullptr}; cudaEvent_t done[2] = {nullptr, nullptr}; bool pending[2] = {false, false}; int cur = 0; };
+  SideBuf sb_dz, sb_dzm, sb_dh, sb_dqkv, sb_dq2;
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  bool side_on = true, side_dirty = false;
+  int sb_write(SideBuf& b, bf16** out);
+  int side_launch_begin(cudaStream_t* s);
+  int side_launch_end(const void* read_ptr);
+  int join_side();
   bool dropout_on = false; unsigned long long dropout_seed = 0x5EEDull;
   bf16 *dzm = nullptr, *dsub = nullptr;
   bf16 *dA = nullptr, *dB = nullptr, *dz = nullptr, *dctx = nullptr, *dq2 = nullptr, *dh = nullptr, *dqkv = nullptr;
