@@ -288,6 +288,7 @@ def main():
            "d2h_bytes_per_step": 24, "ms_per_step": e2e_ms / Ksteps, "timer": "host wall clock around K synchronous calls, max over ranks"}
 
     if rank != 0:
+        model.close()
         if world > 1: dist.destroy_process_group()
         return
     peak_tf, peak_hbm, peak_src = measured_peaks()
@@ -309,6 +310,7 @@ def main():
         cb, _ = cpu_reference(args.config, cfg, 2, 1, sample)
         line["cpu_baseline"] = cb
     print(json.dumps(line), flush=True)
+    model.close()
     if world > 1: dist.destroy_process_group()
 
 

@@ -13,6 +13,7 @@
 #include <nccl.h>
 
 #include <cmath>
+#include <cstdio>
 #include <cstring>
 
 namespace b200xf {
@@ -332,12 +333,16 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
   if (const char* e = getenv("B200XF_SIDE_WGRAD")) side_on = atoi(e) != 0;
+  if (const char* e = getenv("B200XF_PHASE_TIMING")) phase_timing = atoi(e) != 0;
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_ready, cudaEventDisableTiming));
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_done, cudaEventDisableTiming));
   return 0;
 }
 
 Context::~Context() {
+  if (phase_timing && phase_n > 0)
+    fprintf(stderr, "[b200xf] phases over %ld steps (ms): forward %.3f  loss %.3f  backward %.3f  update+join %.3f\n", phase_n,
+            phase_ms[0] / phase_n, phase_ms[1] / phase_n, phase_ms[2] / phase_n, phase_ms[3] / phase_n);
   if (comm) comm_destroy();
   cudaSetDevice(device);
   if (stream) cudaStreamSynchronize(stream);
@@ -726,6 +731,20 @@ int Context::section_done() {
 }
 
 // ------------------------------------------------------------------------------------ steps
+int Context::phase_mark(int i) {
+  if (!phase_timing) return 0;
+  if (i == 0 && phase_n >= 0 && ev_phase[0]) {
+    // fold in the previous step's intervals (its events have long completed when the next step starts)
+    if (cudaEventQuery(ev_phase[4]) == cudaSuccess) {
+      for (int k = 0; k < 4; ++k) { float ms = 0.f; if (cudaEventElapsedTime(&ms, ev_phase[k], ev_phase[k + 1]) == cudaSuccess) phase_ms[k] += ms; }
+      ++phase_n;
+    }
+  }
+  if (!ev_phase[i]) B200XF_CUDA(cudaEventCreate(&ev_phase[i]));
+  B200XF_CUDA(cudaEventRecord(ev_phase[i], stream));
+  return 0;
+}
+
 int Context::loss_and_grad(int Nt, int workers_count, int write_grad) {
   const float inv_w = 1.0f / float(workers_count);
   B200XF_TRY(vocab_ce_fwd_bwd(logits, final_layer.ld, tok_labels, Nt, final_layer.N, nonpad_count, inv_w, row_loss, row_correct,
@@ -742,14 +761,18 @@ int Context::step_device(const long long* inp, const long long* target, int B, i
   B200XF_TRY(check_shapes(B, S, T));
   if (workers_count <= 0) return set_error("workers_count must be positive");
   B200XF_CUDA(cudaSetDevice(device));
+  B200XF_TRY(phase_mark(0));
   B200XF_TRY(prep_targets(target, tok_tgt_in, tok_labels, nonpad_count, B, T1, stream));
   B200XF_TRY(forward(inp, tok_tgt_in, B, S, T, nullptr, mode != 0));
+  B200XF_TRY(phase_mark(1));
   B200XF_TRY(loss_and_grad(B * T, workers_count, mode != 0));
+  B200XF_TRY(phase_mark(2));
   if (mode >= 1) {
     overlap_update = (mode == 2) && (comm != nullptr || overlap_single);
     bucket_begin = 0;
     B200XF_TRY(backward(inp, tok_tgt_in, B, S, T));
   }
+  B200XF_TRY(phase_mark(3));
   if (mode == 2) {
     // metrics: local values stay in metrics[0..2]; the cross-replica sums go to metrics[3..5]
     B200XF_CUDA(cudaMemcpyAsync(metrics + 3, metrics, 3 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
@@ -769,6 +792,7 @@ int Context::step_device(const long long* inp, const long long* target, int B, i
   } else {
     B200XF_CUDA(cudaMemcpyAsync(metrics + 3, metrics, 3 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
   }
+  B200XF_TRY(phase_mark(4));
   if (out6) B200XF_CUDA(cudaMemcpyAsync(out6, metrics, 6 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
   return 0;
 }

@@ -60,6 +60,9 @@ struct Context {
   int side_launch_begin(cudaStream_t* s);
   int side_launch_end(const void* read_ptr);
   int join_side();
+  // optional phase timing (B200XF_PHASE_TIMING=1): events after forward / loss / backward / update, averaged at destroy
+  bool phase_timing = false; cudaEvent_t ev_phase[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}; double phase_ms[4] = {0, 0, 0, 0}; long phase_n = 0;
+  int phase_mark(int i);
   bool dropout_on = false; unsigned long long dropout_seed = 0x5EEDull;
   bf16 *dzm = nullptr, *dsub = nullptr;
   bf16 *dA = nullptr, *dB = nullptr, *dz = nullptr, *dctx = nullptr, *dq2 = nullptr, *dh = nullptr, *dqkv = nullptr;
@@ -77,7 +80,7 @@ struct Context {
   cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
   size_t bucket_bytes = size_t(32) << 20, bucket_begin = 0, next_section = 0;
   bool overlap_update = false;
-  bool overlap_single = false;  // single GPU: run each bucket's Adam on the side stream under the rest of backward (B200XF_OVERLAP_UPDATE=1)
+  bool overlap_single = true;   // single GPU too: each bucket's Adam runs on the update stream under the rest of backward (B200XF_OVERLAP_UPDATE=0 disables)
 
   ~Context();
   int init(const b200xf_hparams& h, int dev, cudaStream_t s);

@@ -206,12 +206,16 @@ class Transformer:
             check(_lib.load().b200xf_params_changed(self._ctx))
             self._dirty = False
 
+    def close(self):
+        """Release the device context (weights, optimizer state, workspace)."""
+        if self._ctx is not None:
+            self._flats = {}
+            _lib.load().b200xf_ctx_destroy(self._ctx)
+            self._ctx = None
+
     def __del__(self):
         try:
-            if self._ctx is not None:
-                self._flats = {}
-                _lib.load().b200xf_ctx_destroy(self._ctx)
-                self._ctx = None
+            self.close()
         except Exception:
             pass
 
