@@ -39,7 +39,7 @@ struct Cfg {
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kSmem = kStages * kStageBytes + 4 * 2 * 4096 /*store staging*/ + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kSmem = kStages * kStageBytes + 4 * 2 * 4096 /*store staging*/ + 1024 /*bias slice*/ + 1024 /*align slack*/ + 256 /*barriers*/;
   static constexpr int kTmemCols = 2 * BN;  // double-buffered accumulator
 };
 
@@ -55,18 +55,12 @@ struct GemmParams {
 };
 
 // bias add, ReLU, residual add / ReLU mask on 32 accumulator columns [col0, col0+32) of one output row.
-__device__ __forceinline__ void epilogue_math(float* f, const GemmParams& p, int row, bool row_ok, int col0, bool add_bias) {
-  const bool full = col0 + 32 <= p.N;
-  if (add_bias) {
-    if (full) {
+__device__ __forceinline__ void epilogue_math(float* f, const GemmParams& p, int row, bool row_ok, int col0, const float* sbias) {
+  if (sbias) {  // this tile's bias slice, staged in shared memory once per tile (zero past N): broadcast reads
 #pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
-        f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j) if (col0 + j < p.N) f[j] += __ldg(p.bias + col0 + j);
+    for (int j = 0; j < 32; j += 4) {
+      const float4 b = *reinterpret_cast<const float4*>(sbias + j);
+      f[j] += b.x; f[j + 1] += b.y; f[j + 2] += b.z; f[j + 3] += b.w;
     }
   }
   if (p.relu) {
@@ -119,7 +113,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* stage_base = smem + C::kStages * C::kStageBytes;  // 4 epilogue warps x 2 x 4 KB store staging
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_base + 4 * 2 * 4096);
+  float* sbias = reinterpret_cast<float*>(stage_base + 4 * 2 * 4096);  // [256] bias slice of the current tile
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sbias + 256);
   uint64_t* empty_bar = full_bar + C::kStages;
   uint64_t* tmem_full = empty_bar + C::kStages;
   uint64_t* tmem_empty = tmem_full + 2;
@@ -230,6 +225,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const bool row_ok = row < p.M;
       const uint32_t taddr = tmem_base + as * BN + (uint32_t(quarter * 32) << 16);
       const bool add_bias = p.bias != nullptr && z == 0;
+      if (add_bias) {  // CTA-uniform: the four epilogue warps stage this tile's BN bias values once
+        asm volatile("bar.sync 1, 128;" ::: "memory");   // everyone is done with the previous tile's slice
+        for (int j = threadIdx.x - 64; j < BN; j += 128) sbias[j] = (tn * BN + j < p.N) ? __ldg(p.bias + tn * BN + j) : 0.f;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
       if (p.d_tma) {
         // TMEM -> registers -> 128B-swizzled staging tile (32 rows x 128 B per warp, double buffered) -> TMA store /
         // TMA reduce-add: coalesced, asynchronous, clipped to the tensor bounds by the hardware.
@@ -252,7 +252,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             float f[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
-            if (col0 < p.N) epilogue_math(f, p, row, row_ok, col0, add_bias);
+            if (col0 < p.N) epilogue_math(f, p, row, row_ok, col0, add_bias ? sbias + (c0 + cc) * 32 : nullptr);
             if (p.d_fp32) {
 #pragma unroll
               for (int q = 0; q < 8; ++q)  // 8 x 16-byte chunks per 128-byte row, XOR-swizzled by the row index
@@ -288,7 +288,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
-        epilogue_math(f, p, row, row_ok, col0, add_bias);
+        epilogue_math(f, p, row, row_ok, col0, add_bias ? sbias + c * 32 : nullptr);
         if (row_ok) {
           if (p.d_fp32) {
             float* dp = reinterpret_cast<float*>(p.d) + size_t(row) * p.ldd + col0;
