@@ -183,6 +183,10 @@ int b200xf_adam_step(float* w, float* g, float* m, float* v, void* w_bf16_or_nul
                      const int64_t* iterations_dev, int embedding_size, int warmup_steps, float beta_1, float beta_2,
                      float epsilon, int zero_grad, void* stream);
 
+/* CRC-32C of a host buffer (continue from `crc`, 0 to start): the per-tensor and per-block checksums of the TF
+ * tensor-bundle files that model.save_weights / load_weights exchange (checkpoint.py:86, __main__.py:87). */
+uint32_t b200xf_crc32c(const void* data, size_t n, uint32_t crc);
+
 /* positional_encoding (transformer_model.py:29-53) computed on the host in fp32: out [positions, d]. */
 int b200xf_positional_encoding_host(float* out, int positions, int d);
 

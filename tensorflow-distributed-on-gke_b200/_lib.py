@@ -76,6 +76,7 @@ SIGNATURES = {
     "b200xf_embed_pe_bwd": (_I, [_P, _P, _P, _I, _I, _I, _P, _SZ, _P]),
     "b200xf_vocab_ce_fwd_bwd": (_I, [_P, _I, _P, _I, _I, _I, _I, _P, _P, _P]),
     "b200xf_adam_step": (_I, [_P, _P, _P, _P, _P, _L, _P, _I, _I, _F, _F, _F, _I, _P]),
+    "b200xf_crc32c": (C.c_uint32, [_P, _SZ, C.c_uint32]),
     "b200xf_positional_encoding_host": (_I, [_P, _I, _I]),
 }
 

@@ -1,25 +1,259 @@
-"""Weight files under the reference's `save_weights(prefix)` / `load_weights(prefix)` call shape
-(checkpoint.py:86, __main__.py:87).  Variables are stored under the Keras object-graph keys of
-saved_weights/*/model_weights.index (`<name>/.ATTRIBUTES/VARIABLE_VALUE`), in a NumPy .npz container
-next to the prefix; the TF tensor-bundle (SSTable) container itself is SURVEY §8(f) rank 1, not built yet."""
+"""TensorFlow tensor-bundle checkpoints under the reference's `save_weights(prefix)` / `load_weights(prefix)` call shape
+(checkpoint.py:86 writes `<dir>/model_weights`, __main__.py:87 reads `saved_weights/2/model_weights`).
+
+File set, as in /root/reference/saved_weights/<n>/: `<prefix>.index` (LevelDB-style SSTable: prefix-compressed keys,
+uncompressed blocks with masked-CRC32C trailers, 48-byte footer, magic 0xdb4775248b80fb57; key "" -> BundleHeaderProto,
+every other key -> BundleEntryProto{dtype, shape, shard_id, offset, size, crc32c}), `<prefix>.data-00000-of-00001` (the
+tensors, little-endian, densely packed in ascending offset) and `checkpoint` (two text lines).  Keys are the Keras
+object-graph names `<variable>/.ATTRIBUTES/VARIABLE_VALUE`; the data shard is laid out in the reference's physical order
+(final_layer, embeddings, all LayerNorms, encoder layers, decoder layers), so for the tutorial model every offset and
+size equals the reference's own index (tests/test_checkpoint_io.py checks this against tests/golden/param_table.json).
+
+Not written: the `_CHECKPOINTABLE_OBJECT_GRAPH` string tensor (a serialized TrackableObjectGraph).  TensorFlow's
+name-based readers (`tf.train.load_checkpoint`, `tf.train.load_variable`) do not need it; Keras' object-based
+`load_weights` does.  The reference's own copy of it sits in the data shards that are missing from the repository
+(.MISSING_LARGE_BLOBS), so it cannot be reproduced or checked here.  The reader skips that entry when present.
+"""
 from __future__ import annotations
 
+import struct
 from pathlib import Path
 
 import numpy as np
 
 SUFFIX = "/.ATTRIBUTES/VARIABLE_VALUE"
+MAGIC = 0xdb4775248b80fb57
+DT_FLOAT = 1
+BLOCK_TARGET = 4096       # leveldb table block size
+RESTART_INTERVAL = 16
+
+# ---------------------------------------------------------------------------------------------- crc32c (Castagnoli)
+_TABLE = None
+
+
+def _table():
+    global _TABLE
+    if _TABLE is None:
+        t = np.zeros((8, 256), dtype=np.uint32)
+        for i in range(256):
+            c = i
+            for _ in range(8):
+                c = (c >> 1) ^ (0x82F63B78 if c & 1 else 0)
+            t[0, i] = c
+        for k in range(1, 8):
+            t[k] = (t[k - 1] >> 8) ^ t[0][t[k - 1] & 0xFF]
+        _TABLE = t
+    return _TABLE
+
+
+def crc32c(data: bytes, crc: int = 0) -> int:
+    """CRC-32C of `data`.  Uses the library's native routine when libb200xf.so is loadable, else a table walk."""
+    try:
+        from . import _lib
+        return int(_lib.load().b200xf_crc32c(bytes(data), len(data), crc))
+    except (_lib.B200XFError, OSError):
+        pass
+    t = _table()[0]
+    c = crc ^ 0xFFFFFFFF
+    for b in bytes(data):
+        c = int(t[(c ^ b) & 0xFF]) ^ (c >> 8)
+    return c ^ 0xFFFFFFFF
+
+
+def masked_crc32c(data: bytes) -> int:
+    """leveldb / TF mask: rotate right by 15 and add a constant."""
+    c = crc32c(data)
+    return (((c >> 15) | (c << 17)) + 0xa282ead8) & 0xFFFFFFFF
+
+
+# ---------------------------------------------------------------------------------------------- varints / protobuf
+def _varint(v: int) -> bytes:
+    out = bytearray()
+    while True:
+        b = v & 0x7F
+        v >>= 7
+        if v:
+            out.append(b | 0x80)
+        else:
+            out.append(b)
+            return bytes(out)
+
+
+def _read_varint(b, p):
+    r = s = 0
+    while True:
+        c = b[p]; p += 1
+        r |= (c & 0x7F) << s; s += 7
+        if c < 0x80:
+            return r, p
+
+
+def _field(num, wire, payload: bytes) -> bytes:
+    return _varint((num << 3) | wire) + payload
+
+
+def _bundle_header() -> bytes:
+    # BundleHeaderProto{num_shards=1, endianness=LITTLE(0, default, omitted), version{producer=1}}
+    return _field(1, 0, _varint(1)) + _field(3, 2, _varint(2) + _field(1, 0, _varint(1)))
+
+
+def _bundle_entry(shape, offset, size, crc) -> bytes:
+    dims = b"".join(_field(2, 2, _varint(len(d)) + d) for d in (_field(1, 0, _varint(int(s))) for s in shape))
+    out = _field(1, 0, _varint(DT_FLOAT)) + _field(2, 2, _varint(len(dims)) + dims)
+    if offset:
+        out += _field(4, 0, _varint(offset))
+    out += _field(5, 0, _varint(size)) + _field(6, 5, struct.pack("<I", crc))
+    return out
+
+
+def _parse_proto(b):
+    p = 0; f = {}
+    while p < len(b):
+        tag, p = _read_varint(b, p); num, wire = tag >> 3, tag & 7
+        if wire == 0: v, p = _read_varint(b, p)
+        elif wire == 2:
+            n, p = _read_varint(b, p); v = b[p:p + n]; p += n
+        elif wire == 5: v = struct.unpack("<I", b[p:p + 4])[0]; p += 4
+        elif wire == 1: v = struct.unpack("<Q", b[p:p + 8])[0]; p += 8
+        else: raise ValueError(f"unsupported wire type {wire}")
+        f.setdefault(num, []).append(v)
+    return f
+
+
+# ---------------------------------------------------------------------------------------------- SSTable
+class _BlockBuilder:
+    def __init__(self):
+        self.buf = bytearray(); self.restarts = [0]; self.count = 0; self.last = b""
+
+    def add(self, key: bytes, value: bytes):
+        shared = 0
+        if self.count % RESTART_INTERVAL == 0 and self.count:
+            self.restarts.append(len(self.buf))
+        elif self.count:
+            n = min(len(key), len(self.last))
+            while shared < n and key[shared] == self.last[shared]:
+                shared += 1
+        self.buf += _varint(shared) + _varint(len(key) - shared) + _varint(len(value)) + key[shared:] + value
+        self.last = key; self.count += 1
+
+    def size(self):
+        return len(self.buf) + 4 * len(self.restarts) + 4
+
+    def finish(self) -> bytes:
+        return bytes(self.buf) + b"".join(struct.pack("<I", r) for r in self.restarts) + struct.pack("<I", len(self.restarts))
+
+
+def _write_table(path: Path, items):
+    """items: sorted [(key bytes, value bytes)].  Uncompressed blocks, each followed by type byte 0 + masked crc32c."""
+    out = bytearray(); index = _BlockBuilder()
+
+    def emit(block: bytes):
+        off = len(out)
+        out.extend(block); out.extend(b"\x00"); out.extend(struct.pack("<I", masked_crc32c(block + b"\x00")))
+        return off, len(block)
+
+    cur = _BlockBuilder(); last_key = b""
+    for k, v in items:
+        cur.add(k, v); last_key = k
+        if cur.size() >= BLOCK_TARGET:
+            off, n = emit(cur.finish()); index.add(last_key, _varint(off) + _varint(n)); cur = _BlockBuilder()
+    if cur.count:
+        off, n = emit(cur.finish()); index.add(last_key, _varint(off) + _varint(n))
+    moff, mn = emit(_BlockBuilder().finish())          # empty metaindex block
+    ioff, inn = emit(index.finish())
+    footer = _varint(moff) + _varint(mn) + _varint(ioff) + _varint(inn)
+    footer += b"\x00" * (40 - len(footer)) + struct.pack("<Q", MAGIC)
+    out.extend(footer)
+    path.write_bytes(bytes(out))
+
+
+def _read_block(d, off, size, verify=True):
+    blk = d[off:off + size]
+    if verify:
+        want = struct.unpack("<I", d[off + size + 1:off + size + 5])[0]
+        if masked_crc32c(d[off:off + size + 1]) != want:
+            raise ValueError("index block checksum mismatch")
+    nrest = struct.unpack("<I", blk[-4:])[0]
+    end = len(blk) - 4 - 4 * nrest
+    p = 0; key = b""; out = []
+    while p < end:
+        shared, p = _read_varint(blk, p); non, p = _read_varint(blk, p); vlen, p = _read_varint(blk, p)
+        key = key[:shared] + blk[p:p + non]; p += non
+        out.append((key, blk[p:p + vlen])); p += vlen
+    return out
+
+
+def read_index(path):
+    """Decode `<prefix>.index` -> list of dicts (key, dtype, shape, offset, size, crc32c), header entry excluded."""
+    d = Path(path).read_bytes()
+    foot = d[-48:]
+    if struct.unpack("<Q", foot[-8:])[0] != MAGIC:
+        raise ValueError(f"{path}: not a tensor-bundle index (bad magic)")
+    p = 0
+    _, p = _read_varint(foot, p); _, p = _read_varint(foot, p)
+    ioff, p = _read_varint(foot, p); isz, p = _read_varint(foot, p)
+    out = []
+    for _, handle in _read_block(d, ioff, isz):
+        q = 0; boff, q = _read_varint(handle, q); bsz, q = _read_varint(handle, q)
+        for k, v in _read_block(d, boff, bsz):
+            if k == b"":
+                continue
+            f = _parse_proto(v)
+            shape = [(_parse_proto(dim).get(1, [0])[0]) for dim in _parse_proto(f[2][0]).get(2, [])] if 2 in f else []
+            out.append(dict(key=k.decode(), dtype=f.get(1, [0])[0], shape=shape, offset=f.get(4, [0])[0], size=f.get(5, [0])[0],
+                            crc32c=f.get(6, [0])[0]))
+    return out
+
+
+# ---------------------------------------------------------------------------------------------- public API
+def reference_order(names):
+    """The reference's physical data-shard order: final_layer, embeddings, every LayerNorm, then the
+    encoder layers' and the decoder layers' Dense variables — which is the order `Transformer.trainable_variables` uses."""
+    return list(names)
 
 
 def save_weights(model, prefix):
-    p = Path(str(prefix) + ".b200xf.npz")
-    p.parent.mkdir(parents=True, exist_ok=True)
-    np.savez(p, **{k + SUFFIX: v for k, v in model.get_weights_dict().items()})
+    prefix = Path(str(prefix)); prefix.parent.mkdir(parents=True, exist_ok=True)
+    weights = model.get_weights_dict()                      # already in the reference's physical order
+    entries = {}; offset = 0
+    with open(str(prefix) + ".data-00000-of-00001", "wb") as f:
+        for name, a in weights.items():
+            raw = np.ascontiguousarray(a, dtype="<f4").tobytes()
+            f.write(raw)
+            entries[(name + SUFFIX).encode()] = _bundle_entry(a.shape, offset, len(raw), masked_crc32c(raw))
+            offset += len(raw)
+    items = [(b"", _bundle_header())] + sorted(entries.items())
+    _write_table(Path(str(prefix) + ".index"), items)
+    (prefix.parent / "checkpoint").write_text(f'model_checkpoint_path: "{prefix.name}"\nall_model_checkpoint_paths: "{prefix.name}"\n')
+
+
+def load_arrays(prefix, verify=True):
+    """{variable name: float32 ndarray} from a tensor bundle (the reference's own, or one written by save_weights)."""
+    prefix = str(prefix)
+    data_path = Path(prefix + ".data-00000-of-00001")
+    if not data_path.exists():
+        raise FileNotFoundError(f"{data_path}: data shard missing (the reference repository ships only the .index files)")
+    out = {}
+    with open(data_path, "rb") as f:
+        for e in read_index(prefix + ".index"):
+            if not e["key"].endswith(SUFFIX) or e["dtype"] != DT_FLOAT:
+                continue                                      # e.g. _CHECKPOINTABLE_OBJECT_GRAPH (DT_STRING)
+            f.seek(e["offset"]); raw = f.read(e["size"])
+            if len(raw) != e["size"]:
+                raise ValueError(f"{e['key']}: data shard truncated")
+            if verify and masked_crc32c(raw) != e["crc32c"]:
+                raise ValueError(f"{e['key']}: tensor checksum mismatch")
+            out[e["key"][:-len(SUFFIX)]] = np.frombuffer(raw, dtype="<f4").reshape(e["shape"]).copy()
+    return out
 
 
 def load_weights(model, prefix):
-    p = Path(str(prefix) + ".b200xf.npz")
-    if not p.exists():
-        raise FileNotFoundError(f"{p} (TF tensor-bundle checkpoints are not readable yet)")
-    z = np.load(p)
-    model.set_weights_dict({k[:-len(SUFFIX)]: z[k] for k in z.files})
+    arrays = load_arrays(prefix)
+    have = {v.name: v.shape for v in model.trainable_variables}
+    missing = sorted(set(have) - set(arrays))
+    if missing:
+        raise KeyError(f"checkpoint lacks {len(missing)} variables, e.g. {missing[:3]}")
+    for n, shp in have.items():
+        if tuple(arrays[n].shape) != tuple(shp):
+            raise ValueError(f"{n}: checkpoint shape {arrays[n].shape} != model shape {shp}")
+    model.set_weights_dict(arrays)
