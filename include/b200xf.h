@@ -75,6 +75,14 @@ int b200xf_get_iterations(b200xf_ctx* ctx, int64_t* iterations);
 int b200xf_forward(b200xf_ctx* ctx, const int64_t* inp, const int64_t* tgt_in, int B, int S, int T, int training,
                    float* logits_out);
 
+/* The second return value of Transformer.call (transformer_model.py:312-313,348): the softmax attention weights of
+ * decoder layer `decoder_layer` (0-based), block 1 = look-ahead self-attention [B,H,T,T], block 2 = cross-attention
+ * [B,H,T,S], fp32 DEVICE buffer, for the batch of the most recent b200xf_forward (whose token buffers must still be
+ * alive).  tester.py:51-52 is the caller in the reference. */
+int b200xf_attention_weights(b200xf_ctx* ctx, int decoder_layer, int block, float* out);
+/* tf.argmax(x, axis=-1) over fp32 DEVICE rows (tester.py:38): out[r] = lowest index of the maximum of row r. */
+int b200xf_argmax_rows(const float* x, int ld, int rows, int cols, int64_t* out, void* stream);
+
 /* ---- train_step (__main__.py:105-117): shift, forward, local_loss_function(.., workers_count), backward,
  * gradient all-reduce when a communicator is attached (cluster/cluster.py:66), Adam + schedule in place,
  * accuracy counts.  inp [B,S], target [B,T+1] int64.  out6 (fp32) = {local loss (already / workers_count),

@@ -85,6 +85,14 @@ int b200xf_dropout_mask(b200xf_ctx* ctx, int site, int rows, int cols, float* ou
   if (!d.thresh) return set_error("dropout is disabled (rate 0)");
   return dropout_mask_fill(out, rows, cols, d, c.stream);
 }
+int b200xf_attention_weights(b200xf_ctx* ctx, int decoder_layer, int block, float* out) {
+  if (!ctx || !out) return set_error("null argument");
+  return ctx->c.attention_weights(decoder_layer, block, out);
+}
+int b200xf_argmax_rows(const float* x, int ld, int rows, int cols, int64_t* out, void* stream) {
+  if (!x || !out) return set_error("null argument");
+  return argmax_rows(x, ld, rows, cols, reinterpret_cast<long long*>(out), static_cast<cudaStream_t>(stream));
+}
 int b200xf_synchronize(b200xf_ctx* ctx) {
   if (!ctx) return set_error("null ctx");
   B200XF_CUDA(cudaStreamSynchronize(ctx->c.stream));

@@ -513,3 +513,46 @@ int attention_bwd(const AttnArgs& a, cudaStream_t stream) {
 }
 
 }  // namespace b200xf
+
+// ------------------------------------------------------------------------------------------------ attention weight maps
+// transformer_model.py:106,312-313: the softmax weights themselves, [B,H,Sq,Sk] fp32, for the inference API
+// (tester.py:51-52 plots them).  Recomputed from Q, K and the row statistics the forward pass saved; not on the training path.
+namespace b200xf {
+namespace {
+__global__ void __launch_bounds__(128)
+attention_probs_kernel(const bf16* __restrict__ q, int ldq, const bf16* __restrict__ k, int ldk, const float* __restrict__ lse,
+                       const long long* __restrict__ key_tokens, int causal, int H, int Sq, int Sk, int dk, float scale_log2,
+                       float* __restrict__ out) {
+  pdl_wait();
+  pdl_trigger();
+  __shared__ float sq[128];
+  const int i = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const bf16* qrow = q + (size_t(b) * Sq + i) * ldq + h * dk;
+  for (int c = threadIdx.x; c < dk; c += blockDim.x) sq[c] = __bfloat162float(qrow[c]);
+  __syncthreads();
+  const float2 ml = reinterpret_cast<const float2*>(lse)[(size_t(b) * H + h) * Sq + i];
+  float* orow = out + ((size_t(b) * H + h) * Sq + i) * Sk;
+  for (int j = threadIdx.x; j < Sk; j += blockDim.x) {
+    const bf16* krow = k + (size_t(b) * Sk + j) * ldk + h * dk;
+    float s = 0.f;
+    for (int c = 0; c < dk; c += 2) {
+      const uint32_t u = *reinterpret_cast<const uint32_t*>(krow + c);
+      s += sq[c] * ptx::bf16_lo(u) + sq[c + 1] * ptx::bf16_hi(u);
+    }
+    float v = s * scale_log2;
+    if (key_tokens[size_t(b) * Sk + j] == 0 || (causal && j > i)) v = kMasked;
+    orow[j] = exp2f((v - ml.x) - ml.y);
+  }
+}
+}  // namespace
+
+int attention_probs(const AttnArgs& a, float* out, cudaStream_t stream) {
+  if (!a.q || !a.k || !a.lse || !a.key_tokens || !out) return set_error("attention_probs: null pointer");
+  if (a.dk > 128 || a.dk % 2) return set_error("attention_probs: head size %d unsupported", a.dk);
+  const float scale_log2 = kLog2e / sqrtf(float(a.dk));
+  B200XF_CUDA(launch_k(attention_probs_kernel, dim3(a.Sq, a.H, a.B), 128, 0, stream, a.q, a.ldq, a.k, a.ldk,
+                       static_cast<const float*>(a.lse), a.key_tokens, a.causal, a.H, a.Sq, a.Sk, a.dk, scale_log2, out));
+  count_launch();
+  return 0;
+}
+}  // namespace b200xf

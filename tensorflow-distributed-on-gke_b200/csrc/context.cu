@@ -491,6 +491,7 @@ int Context::check_shapes(int B, int S, int T) {
 int Context::forward(const long long* inp, const long long* tgt_in, int B, int S, int T, float* logits_f32, bool training) {
   B200XF_TRY(check_shapes(B, S, T));
   dropout_on = training && hp.droput_rate > 0.f;
+  last_B = B; last_S = S; last_T = T; last_inp = inp; last_tgt = tgt_in;
   const int L = hp.layers_count, d = hp.embedding_size, H = hp.heads_count, dk = d / H;
   const int Ns = B * S, Nt = B * T;
   const size_t cap = size_t(hp.max_tokens) * d;
@@ -555,6 +556,23 @@ int Context::forward(const long long* inp, const long long* tgt_in, int B, int S
     B200XF_TRY(dense_fwd(dec_out, Nt, final_layer, logits, 0, nullptr));
   }
   return 0;
+}
+
+// attention weights of decoder layer `layer`, block 1 (causal self-attention, [B,H,T,T]) or 2 (cross, [B,H,T,S]), for
+// the batch of the LAST forward / step call (transformer_model.py:312-313)
+int Context::attention_weights(int layer, int block, float* out) {
+  if (last_B <= 0) return set_error("attention_weights: no forward pass has run yet");
+  if (layer < 0 || layer >= hp.layers_count || (block != 1 && block != 2)) return set_error("attention_weights: bad layer/block");
+  const int d = hp.embedding_size, H = hp.heads_count, dk = d / H;
+  const DecAct& a = da[layer];
+  AttnArgs at;
+  at.B = last_B; at.H = H; at.Sq = last_T; at.dk = dk;
+  if (block == 1) {
+    at.q = a.qkv; at.k = a.qkv + d; at.ldq = at.ldk = 3 * d; at.lse = a.lse1; at.key_tokens = last_tgt; at.causal = 1; at.Sk = last_T;
+  } else {
+    at.q = a.q2; at.ldq = d; at.k = kv + size_t(layer) * 2 * d; at.ldk = kv_all.ld; at.lse = a.lse2; at.key_tokens = last_inp; at.causal = 0; at.Sk = last_S;
+  }
+  return attention_probs(at, out, stream);
 }
 
 // ------------------------------------------------------------------------------------ backward

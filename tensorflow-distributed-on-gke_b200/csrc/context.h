@@ -105,6 +105,8 @@ struct Context {
   int colsum(const bf16* x, int ld, int rows, int cols, size_t dst_off);
   float* red_alloc(size_t floats);
   int flush_reductions();
+  int last_B = 0, last_S = 0, last_T = 0; const long long *last_inp = nullptr, *last_tgt = nullptr;
+  int attention_weights(int layer, int block, float* out);
   int check_shapes(int B, int S, int T);
   int forward(const long long* inp, const long long* tgt_in, int B, int S, int T, float* logits_f32, bool training);
   int backward(const long long* inp, const long long* tgt_in, int B, int S, int T);

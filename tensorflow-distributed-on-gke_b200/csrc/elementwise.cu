@@ -777,6 +777,36 @@ int cast_f32_to_bf16(const float* in, bf16* out, size_t n, cudaStream_t stream) 
   return 0;
 }
 
+namespace {
+// tf.argmax over the last axis (tester.py:38, transformer_model.py:21): lowest index among equal maxima.
+__global__ void __launch_bounds__(256)
+argmax_rows_kernel(const float* __restrict__ x, int ld, int cols, long long* __restrict__ out) {
+  pdl_wait();
+  pdl_trigger();
+  __shared__ float sv[8]; __shared__ int si[8];
+  const float* row = x + size_t(blockIdx.x) * ld;
+  float bv = -INFINITY; int bi = 0x7fffffff;
+  for (int j = threadIdx.x; j < cols; j += blockDim.x) { const float v = row[j]; if (v > bv) { bv = v; bi = j; } }
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, bv, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = bv; si[threadIdx.x >> 5] = bi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) if (sv[w] > bv || (sv[w] == bv && si[w] < bi)) { bv = sv[w]; bi = si[w]; }
+    out[blockIdx.x] = bi;
+  }
+}
+}  // namespace
+
+int argmax_rows(const float* x, int ld, int rows, int cols, long long* out, cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0) return set_error("argmax: empty problem");
+  B200XF_CUDA(launch_k(argmax_rows_kernel, rows, 256, 0, stream, x, ld, cols, out));
+  count_launch();
+  return 0;
+}
+
 int cast_bf16_to_f32_2d(const bf16* in, int ldi, float* out, int ldo, int rows, int cols, cudaStream_t stream) {
   if (rows <= 0 || cols <= 0) return 0;
   const size_t total = size_t(rows) * cols;

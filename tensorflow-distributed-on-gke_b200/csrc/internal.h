@@ -88,6 +88,8 @@ struct AttnArgs {
 };
 int attention_fwd(const AttnArgs& a, cudaStream_t stream);
 int attention_bwd(const AttnArgs& a, cudaStream_t stream);
+// softmax weights [B,H,Sq,Sk] fp32 recomputed from q, k and the saved row statistics (inference API)
+int attention_probs(const AttnArgs& a, float* out, cudaStream_t stream);
 // tcgen05 single-tile path (Sq, Sk <= 128, head size 64); B200XF_ATTENTION_TC=0 disables it
 bool attention_tc_supported(const AttnArgs& a);
 int attention_bwd_tc(const AttnArgs& a, cudaStream_t stream);
@@ -140,6 +142,7 @@ int increment_counter(long long* iterations_dev, cudaStream_t stream);
 int colsum_parts(int rows, int cols);
 int colsum_partial(const bf16* x, int ld, int rows, int cols, float* partials, cudaStream_t stream);
 int cast_f32_to_bf16(const float* in, bf16* out, size_t n, cudaStream_t stream);
+int argmax_rows(const float* x, int ld, int rows, int cols, long long* out, cudaStream_t stream);  // first maximum wins
 int cast_bf16_to_f32_2d(const bf16* in, int ldi, float* out, int ldo, int rows, int cols, cudaStream_t stream);
 
 }  // namespace b200xf

@@ -84,6 +84,53 @@ class _DeviceArray:
         self._owner = owner
 
 
+class AttentionWeights(dict):
+    """The attention_weights dict of Transformer.call (transformer_model.py:312-313): keys
+    `decoder_layer{i}_block1` ([B,H,T,T]) and `decoder_layer{i}_block2` ([B,H,T,S]), i = 1..layers_count.  The maps are
+    computed on first access from the activations of the forward pass that returned this object, so read them before
+    the model runs another batch."""
+
+    def __init__(self, model, inp, tgt):
+        super().__init__()
+        self._model, self._inp, self._tgt = model, inp, tgt   # keeps the token buffers alive
+        self._serial = model._forward_serial
+        self._names = [f"decoder_layer{i + 1}_block{b}" for i in range(model.hparams["layers_count"]) for b in (1, 2)]
+
+    def keys(self):
+        return list(self._names)
+
+    def __iter__(self):
+        return iter(self._names)
+
+    def __len__(self):
+        return len(self._names)
+
+    def __contains__(self, k):
+        return k in self._names
+
+    def items(self):
+        return [(k, self[k]) for k in self._names]
+
+    def values(self):
+        return [self[k] for k in self._names]
+
+    def __getitem__(self, key):
+        if dict.__contains__(self, key):
+            return dict.__getitem__(self, key)
+        if key not in self._names:
+            raise KeyError(key)
+        m = self._model
+        if m._forward_serial != self._serial:
+            raise _lib.B200XFError("attention weights must be read before the model runs another batch")
+        layer = int(key.split("_")[1][len("layer"):]) - 1
+        block = int(key[-1])
+        B, S = self._inp.shape; T = self._tgt.shape[1]
+        out = torch.empty((B, m.hparams["heads_count"], T, T if block == 1 else S), device=m.device, dtype=torch.float32)
+        check(_lib.load().b200xf_attention_weights(m._ctx, layer, block, ptr(out)))
+        dict.__setitem__(self, key, out)
+        return out
+
+
 # ------------------------------------------------------------------ the model
 class Transformer:
     """transformer_model.py:318-363 — Transformer(layers_count, embedding_size, heads_count,
@@ -125,6 +172,7 @@ class Transformer:
         self._dirty = False
         self.variables = []
         self._comm = None
+        self._forward_serial = 0
 
     # ---- context management ---------------------------------------------------------------
     def _create_ctx(self, max_tokens):
@@ -269,9 +317,10 @@ class Transformer:
         T = tgt.shape[1]
         self._ensure_built(max(B * S, B * T))
         self._sync_weights()
+        self._forward_serial += 1
         logits = torch.empty((B, T, self.hparams["target_vocabulary_size"]), device=self.device, dtype=torch.float32)
         check(_lib.load().b200xf_forward(self._ctx, ptr(inp), ptr(tgt), B, S, T, int(bool(training)), ptr(logits)))
-        return logits, {}
+        return logits, AttentionWeights(self, inp, tgt)
 
     call = __call__
 
@@ -282,6 +331,7 @@ class Transformer:
         T1 = target.shape[1]
         self._ensure_built(max(B * S, B * T1))
         self._sync_weights()
+        self._forward_serial += 1
         out = torch.empty(6, device=self.device, dtype=torch.float32)
         check(fn(self._ctx, ptr(inp), ptr(target), B, S, T1, *extra, ptr(out)))
         return out
@@ -348,6 +398,29 @@ class Transformer:
         from pathlib import Path
         Path(path).mkdir(parents=True, exist_ok=True)
         self.save_weights(str(Path(path) / "variables" / "variables"))
+
+
+def greedy_decode(transformer, encoder_input, start_id, end_id, max_length=20):
+    """The decode loop of tester.py:13-53 without its tokenizers: starting from `start_id`, feed the growing target back
+    through the model (the reference re-encodes the source every step; so does this), append the argmax of the last
+    position, stop at `end_id` or after `max_length` tokens.  Returns (tokens [1, n] int64 on the device,
+    attention_weights of the final pass over output[:, :-1])."""
+    enc = _cuda_tokens(encoder_input, transformer.device)
+    if enc.dim() == 1:
+        enc = enc[None, :]
+    assert enc.shape[0] == 1, "greedy_decode handles one sentence, as the reference's Tester"
+    out = torch.full((1, 1), int(start_id), device=transformer.device, dtype=torch.int64)
+    V = transformer.hparams["target_vocabulary_size"]
+    nxt = torch.empty(1, device=transformer.device, dtype=torch.int64)
+    for _ in range(int(max_length)):
+        logits, _ = transformer([enc, out], training=False)
+        last = logits[0, -1]
+        check(_lib.load().b200xf_argmax_rows(ptr(last), V, 1, V, ptr(nxt), _lib.stream_ptr()))
+        out = torch.cat([out, nxt[None, :]], dim=1)
+        if int(nxt.item()) == int(end_id):
+            break
+    _, weights = transformer([enc, out[:, :-1]], training=False)
+    return out, weights
 
 
 def build_model(transformer):
