@@ -211,12 +211,146 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
   if (warp == 1) { ptx::tc_fence_after(); ptx::tmem_dealloc(tmem, 512); }
 }
 
+// ---------------------------------------------------------------------------------------------------------- forward
+// S = Q K^T (TMEM) -> one thread per query row: mask, max, exp2, sum -> P (bf16, swizzled smem) -> O = P V (TMEM) -> O / sum.
+// 80 KB of shared memory and 256 TMEM columns, so two CTAs share an SM.
+constexpr int kSmemFwd = 3 * kTileBytes + kPBytes + 1024 + 1024;
+
+__global__ void __launch_bounds__(kThreads, 2)
+attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                   const __grid_constant__ CUtensorMap tm_v, const TcArgs p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem; uint8_t* sK = sQ + kTileBytes; uint8_t* sV = sK + kTileBytes; uint8_t* sP = sV + kTileBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kPBytes);  // 0 load, 1 S ready, 2 P written, 3 O ready
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+  int* s_mask = reinterpret_cast<int*>(bars + 6);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int h = blockIdx.x, b = blockIdx.y;
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tm_q); ptx::prefetch_tmap(&tm_k); ptx::prefetch_tmap(&tm_v);
+    ptx::mbar_init(&bars[0], 1); ptx::mbar_init(&bars[1], 1); ptx::mbar_init(&bars[2], 128); ptx::mbar_init(&bars[3], 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) { ptx::tmem_alloc(tmem_slot, 256); ptx::tmem_relinquish(); }
+  pdl_wait();
+  pdl_trigger();
+  if (warp >= 2) {
+    const int j = threadIdx.x - 64;
+    s_mask[j] = (j >= p.Sk) ? 2 : (p.key_tokens[size_t(b) * p.Sk + j] == 0 ? 1 : 0);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tO = tmem + 128;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      ptx::mbar_expect_tx(&bars[0], 3 * kTileBytes);
+      ptx::tma_load_2d(sQ, &tm_q, &bars[0], h * kD, b * p.Sq);
+      ptx::tma_load_2d(sK, &tm_k, &bars[0], h * kD, b * p.Sk);
+      ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
+      ptx::mbar_wait(&bars[0], 0);
+      ptx::tc_fence_after();
+      constexpr uint32_t idesc_kk = ptx::make_idesc_bf16(128, 128, 0, 0);
+      const uint32_t aQ = ptx::smem_u32(sQ), aK = ptx::smem_u32(sK), aV = ptx::smem_u32(sV), aP = ptx::smem_u32(sP);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        ptx::umma_bf16(tS, ptx::make_smem_desc(aQ + k * 32, 16, 1024), ptx::make_smem_desc(aK + k * 32, 16, 1024), idesc_kk, k > 0);
+      ptx::umma_commit(&bars[1]);
+      ptx::mbar_wait(&bars[2], 0);
+      ptx::tc_fence_after();
+      constexpr uint32_t idesc_km = ptx::make_idesc_bf16(128, 64, 0, 1);  // A = P [m=q][k=key], B = V [k=key][n=dk]
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        ptx::umma_bf16(tO, ptx::make_smem_desc(aP + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
+                       ptx::make_smem_desc(aV + k * 2048, kTileBytes, 1024), idesc_km, k > 0);
+      ptx::umma_commit(&bars[3]);
+    }
+  } else if (warp >= 2) {
+    const int quarter = warp & 3;
+    const int i = quarter * 32 + lane;
+    const uint32_t lane_base = uint32_t(quarter * 32) << 16;
+    ptx::mbar_wait(&bars[1], 0);
+    ptx::tc_fence_after();
+    const bool row_ok = i < p.Sq;
+    float s[kT];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      tmem_ld32(tS + lane_base + c * 32, s + c * 32);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int key = c * 32 + j;
+        const int mk = s_mask[key];
+        float v = s[key] * p.scale_log2;
+        if (mk == 1 || (p.causal && key > i)) v = kMasked;
+        if (mk == 2) v = -INFINITY;
+        s[key] = v;
+        mx = fmaxf(mx, v);
+      }
+    }
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < kT; ++j) { s[j] = exp2f(s[j] - mx); sum += s[j]; }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) store_row32(sP, i, c * 32, s + c * 32);
+    ptx::tc_fence_before();
+    ptx::fence_proxy_async();
+    ptx::mbar_arrive(&bars[2]);
+
+    ptx::mbar_wait(&bars[3], 0);
+    ptx::tc_fence_after();
+    const float inv = 1.0f / sum;
+    bf16* dst = p.o + (size_t(b) * p.Sq + (row_ok ? i : 0)) * p.ldo + h * kD;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      float f[32];
+      tmem_ld32(tO + lane_base + c * 32, f);
+      if (row_ok) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 u;
+          u.x = ptx::pack_bf16x2(f[q * 8] * inv, f[q * 8 + 1] * inv); u.y = ptx::pack_bf16x2(f[q * 8 + 2] * inv, f[q * 8 + 3] * inv);
+          u.z = ptx::pack_bf16x2(f[q * 8 + 4] * inv, f[q * 8 + 5] * inv); u.w = ptx::pack_bf16x2(f[q * 8 + 6] * inv, f[q * 8 + 7] * inv);
+          *reinterpret_cast<uint4*>(dst + c * 32 + q * 8) = u;
+        }
+      }
+    }
+    if (row_ok && p.lse) reinterpret_cast<float2*>(p.lse)[(size_t(b) * p.H + h) * p.Sq + i] = make_float2(mx, log2f(sum));
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { ptx::tc_fence_after(); ptx::tmem_dealloc(tmem, 256); }
+}
+
 }  // namespace
 
 bool attention_tc_supported(const AttnArgs& a) {
   static int enabled = -1;
   if (enabled < 0) { const char* e = getenv("B200XF_ATTENTION_TC"); enabled = (e && atoi(e) == 0) ? 0 : 1; }
   return enabled && a.dk == kD && a.Sq <= kT && a.Sk <= kT && a.Sq > 0 && a.Sk > 0;
+}
+
+int attention_fwd_tc(const AttnArgs& a, cudaStream_t stream) {
+  CUtensorMap tq, tk, tv;
+  const uint64_t cols = uint64_t(a.H) * kD;
+  B200XF_TRY(tensor_map_2d(a.q, cols, uint64_t(a.B) * a.Sq, a.ldq, kT, &tq, 0));
+  B200XF_TRY(tensor_map_2d(a.k, cols, uint64_t(a.B) * a.Sk, a.ldk, kT, &tk, 0));
+  B200XF_TRY(tensor_map_2d(a.v, cols, uint64_t(a.B) * a.Sk, a.ldv, kT, &tv, 0));
+  TcArgs p{};
+  p.key_tokens = a.key_tokens; p.o = a.o; p.ldo = a.ldo; p.lse = a.lse;
+  p.H = a.H; p.Sq = a.Sq; p.Sk = a.Sk; p.causal = a.causal;
+  p.scale = 1.0f / sqrtf(float(a.dk)); p.scale_log2 = p.scale * kLog2e;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] { attr_err = cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemFwd); });
+  if (attr_err != cudaSuccess) return set_error("cudaFuncSetAttribute(attn_fwd_tc): %s", cudaGetErrorString(attr_err));
+  B200XF_CUDA(launch_k(attn_fwd_tc_kernel, dim3(a.H, a.B), kThreads, kSmemFwd, stream, tq, tk, tv, p));
+  count_launch();
+  return 0;
 }
 
 int attention_bwd_tc(const AttnArgs& a, cudaStream_t stream) {

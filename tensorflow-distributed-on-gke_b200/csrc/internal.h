@@ -92,6 +92,7 @@ int attention_bwd(const AttnArgs& a, cudaStream_t stream);
 int attention_probs(const AttnArgs& a, float* out, cudaStream_t stream);
 // tcgen05 single-tile path (Sq, Sk <= 128, head size 64); B200XF_ATTENTION_TC=0 disables it
 bool attention_tc_supported(const AttnArgs& a);
+int attention_fwd_tc(const AttnArgs& a, cudaStream_t stream);
 int attention_bwd_tc(const AttnArgs& a, cudaStream_t stream);
 
 // ---- LayerNorm (+ optional residual add) fwd / bwd (transformer_model.py:187-188,198,204)
