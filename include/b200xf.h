@@ -8,8 +8,10 @@
  *
  * Conventions: every function returns 0 on success and non-zero on failure, after which
  * b200xf_last_error() (thread-local) describes the problem.  Tokens are int64, row-major [batch, seq],
- * PAD = 0 (transformer_model.py:12,22,60).  Dense kernels are [in, out] (y = xW + b).  All device work is
- * enqueued on the context's stream and is asynchronous unless stated.  A context is not thread-safe;
+ * PAD = 0 (transformer_model.py:12,22,60).  Dense kernels are [in, out] (y = xW + b).  Device work runs on
+ * streams the context owns; each call first orders them after the caller's stream (the one given to
+ * b200xf_ctx_create) and then orders the caller's stream after them, so the caller sees plain stream
+ * semantics.  Calls are asynchronous unless stated.  A context is not thread-safe;
  * distinct contexts are independent (one per GPU / process, as one TF worker per pod in the reference).
  */
 #ifndef B200XF_H_

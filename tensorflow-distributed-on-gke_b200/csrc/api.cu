@@ -42,37 +42,55 @@ float* b200xf_param_ptr(b200xf_ctx* ctx) { return ctx ? ctx->c.params : nullptr;
 float* b200xf_grad_ptr(b200xf_ctx* ctx) { return ctx ? ctx->c.grads : nullptr; }
 float* b200xf_adam_m_ptr(b200xf_ctx* ctx) { return ctx ? ctx->c.adam_m : nullptr; }
 float* b200xf_adam_v_ptr(b200xf_ctx* ctx) { return ctx ? ctx->c.adam_v : nullptr; }
-int b200xf_params_changed(b200xf_ctx* ctx) { return ctx ? ctx->c.params_changed() : set_error("null ctx"); }
-int b200xf_set_iterations(b200xf_ctx* ctx, int64_t it) { return ctx ? ctx->c.set_iterations(it) : set_error("null ctx"); }
+#define B200XF_SCOPED(ctx, expr)            \
+  do {                                      \
+    B200XF_TRY((ctx)->c.enter());           \
+    const int _rc2 = (expr);                \
+    if (_rc2) return _rc2;                  \
+    return (ctx)->c.leave();                \
+  } while (0)
+
+int b200xf_params_changed(b200xf_ctx* ctx) {
+  if (!ctx) return set_error("null ctx");
+  B200XF_SCOPED(ctx, ctx->c.params_changed());
+}
+int b200xf_set_iterations(b200xf_ctx* ctx, int64_t it) {
+  if (!ctx) return set_error("null ctx");
+  B200XF_SCOPED(ctx, ctx->c.set_iterations(it));
+}
 int b200xf_get_iterations(b200xf_ctx* ctx, int64_t* it) {
   if (!ctx || !it) return set_error("null argument");
-  long long v = 0; int rc = ctx->c.get_iterations(&v); *it = v; return rc;
+  long long v = 0;
+  B200XF_TRY(ctx->c.enter());
+  int rc = ctx->c.get_iterations(&v);
+  *it = v;
+  return rc ? rc : ctx->c.leave();
 }
 
 int b200xf_forward(b200xf_ctx* ctx, const int64_t* inp, const int64_t* tgt_in, int B, int S, int T, int training, float* logits_out) {
   if (!ctx || !inp || !tgt_in) return set_error("null argument");
-  if (cudaSetDevice(ctx->c.device) != cudaSuccess) return set_error("cudaSetDevice failed");
-  return ctx->c.forward(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(tgt_in), B, S, T, logits_out, training != 0);
+  B200XF_SCOPED(ctx, ctx->c.forward(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(tgt_in), B, S, T, logits_out, training != 0));
 }
 int b200xf_train_step_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T1, int workers, float* out6) {
   if (!ctx || !inp || !target) return set_error("null argument");
-  return ctx->c.step_device(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(target), B, S, T1, workers, 2, out6);
+  B200XF_SCOPED(ctx, ctx->c.step_device(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(target), B, S, T1, workers, 2, out6));
 }
 int b200xf_train_step_host(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T1, int workers, float* out6) {
   if (!ctx || !inp || !target || !out6) return set_error("null argument");
-  return ctx->c.step_host(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(target), B, S, T1, workers, out6);
+  B200XF_SCOPED(ctx, ctx->c.step_host(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(target), B, S, T1, workers, out6));
 }
 int b200xf_eval_step_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T1, float* out6) {
   if (!ctx || !inp || !target) return set_error("null argument");
-  return ctx->c.step_device(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(target), B, S, T1, 1, 0, out6);
+  B200XF_SCOPED(ctx, ctx->c.step_device(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(target), B, S, T1, 1, 0, out6));
 }
 int b200xf_forward_backward_device(b200xf_ctx* ctx, const int64_t* inp, const int64_t* target, int B, int S, int T1, int workers, float* out6) {
   if (!ctx || !inp || !target) return set_error("null argument");
-  return ctx->c.step_device(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(target), B, S, T1, workers, 1, out6);
+  B200XF_SCOPED(ctx, ctx->c.step_device(reinterpret_cast<const long long*>(inp), reinterpret_cast<const long long*>(target), B, S, T1, workers, 1, out6));
 }
 int b200xf_set_dropout_seed(b200xf_ctx* ctx, uint64_t seed) {
   if (!ctx) return set_error("null ctx");
   ctx->c.dropout_seed = seed;
+  ctx->c.drop_graphs();  // captured steps carry the old key
   return 0;
 }
 int b200xf_dropout_mask(b200xf_ctx* ctx, int site, int rows, int cols, float* out) {
@@ -83,11 +101,11 @@ int b200xf_dropout_mask(b200xf_ctx* ctx, int site, int rows, int cols, float* ou
   const DropArgs d = c.site_drop(site);
   c.dropout_on = saved;
   if (!d.thresh) return set_error("dropout is disabled (rate 0)");
-  return dropout_mask_fill(out, rows, cols, d, c.stream);
+  B200XF_SCOPED(ctx, dropout_mask_fill(out, rows, cols, d, c.stream));
 }
 int b200xf_attention_weights(b200xf_ctx* ctx, int decoder_layer, int block, float* out) {
   if (!ctx || !out) return set_error("null argument");
-  return ctx->c.attention_weights(decoder_layer, block, out);
+  B200XF_SCOPED(ctx, ctx->c.attention_weights(decoder_layer, block, out));
 }
 int b200xf_argmax_rows(const float* x, int ld, int rows, int cols, int64_t* out, void* stream) {
   if (!x || !out) return set_error("null argument");
@@ -97,6 +115,8 @@ int b200xf_synchronize(b200xf_ctx* ctx) {
   if (!ctx) return set_error("null ctx");
   B200XF_CUDA(cudaStreamSynchronize(ctx->c.stream));
   B200XF_CUDA(cudaStreamSynchronize(ctx->c.comm_stream));
+  B200XF_CUDA(cudaStreamSynchronize(ctx->c.side_stream));
+  B200XF_CUDA(cudaStreamSynchronize(ctx->c.user_stream));
   return 0;
 }
 
@@ -108,8 +128,13 @@ int b200xf_comm_init(b200xf_ctx* ctx, const void* id, int rank, int world) {
 int b200xf_comm_destroy(b200xf_ctx* ctx) { return ctx ? ctx->c.comm_destroy() : set_error("null ctx"); }
 int b200xf_allreduce_bucket(b200xf_ctx* ctx, float* ptr, int64_t count) {
   if (!ctx || !ptr) return set_error("null argument");
+  B200XF_TRY(ctx->c.enter());
+  B200XF_CUDA(cudaEventRecord(ctx->c.ev_ready, ctx->c.stream));
+  B200XF_CUDA(cudaStreamWaitEvent(ctx->c.comm_stream, ctx->c.ev_ready, 0));
   B200XF_TRY(ctx->c.allreduce(ptr, size_t(count), ctx->c.comm_stream));
-  return 0;
+  B200XF_CUDA(cudaEventRecord(ctx->c.ev_done, ctx->c.comm_stream));
+  B200XF_CUDA(cudaStreamWaitEvent(ctx->c.stream, ctx->c.ev_done, 0));
+  return ctx->c.leave();
 }
 
 // ---------------------------------------------------------------- per-kernel entry points

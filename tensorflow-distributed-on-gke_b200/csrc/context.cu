@@ -213,7 +213,7 @@ int Context::arena_alloc(T** out, size_t count) {
 }
 
 int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
-  hp = h; device = dev; stream = s;
+  hp = h; device = dev; user_stream = s;
   const int L = hp.layers_count, d = hp.embedding_size, H = hp.heads_count, dff = hp.feed_forward_hidden_size;
   if (L <= 0 || d <= 0 || H <= 0 || dff <= 0) return set_error("invalid hyper-parameters");
   if (d % H) return set_error("embedding_size %% heads_count != 0 (transformer_model.py:117)");
@@ -223,6 +223,13 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   if (!(hp.droput_rate >= 0.f && hp.droput_rate < 1.f)) return set_error("dropout rate %g must be in [0, 1)", hp.droput_rate);
   if (hp.max_tokens <= 0) return set_error("max_tokens must be positive");
   B200XF_CUDA(cudaSetDevice(device));
+  {
+    int least = 0, greatest = 0;
+    B200XF_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    B200XF_CUDA(cudaStreamCreateWithPriority(&stream, cudaStreamNonBlocking, greatest));  // the critical path outranks the side streams
+    B200XF_CUDA(cudaEventCreateWithFlags(&ev_user, cudaEventDisableTiming));
+    B200XF_CUDA(cudaEventCreateWithFlags(&ev_own, cudaEventDisableTiming));
+  }
   build_layout();
   const size_t P = total_params;
   B200XF_CUDA(cudaMalloc(&params, P * sizeof(float)));
@@ -334,18 +341,22 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
   if (const char* e = getenv("B200XF_SIDE_WGRAD")) side_on = atoi(e) != 0;
   if (const char* e = getenv("B200XF_PHASE_TIMING")) phase_timing = atoi(e) != 0;
+  if (const char* e = getenv("B200XF_GRAPH")) use_graph = atoi(e) != 0;
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_ready, cudaEventDisableTiming));
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_done, cudaEventDisableTiming));
   return 0;
 }
 
 Context::~Context() {
+  drop_graphs();
   if (phase_timing && phase_n > 0)
     fprintf(stderr, "[b200xf] phases over %ld steps (ms): forward %.3f  loss %.3f  backward %.3f  update+join %.3f\n", phase_n,
             phase_ms[0] / phase_n, phase_ms[1] / phase_n, phase_ms[2] / phase_n, phase_ms[3] / phase_n);
   if (comm) comm_destroy();
   cudaSetDevice(device);
-  if (stream) cudaStreamSynchronize(stream);
+  if (stream) { cudaStreamSynchronize(stream); cudaStreamDestroy(stream); }
+  if (ev_user) cudaEventDestroy(ev_user);
+  if (ev_own) cudaEventDestroy(ev_own);
   cudaFree(params); cudaFree(grads); cudaFree(adam_m); cudaFree(adam_v); cudaFree(shadow); cudaFree(arena);
   if (host_out) cudaFreeHost(host_out);
   if (comm_stream) cudaStreamDestroy(comm_stream);
@@ -370,6 +381,18 @@ int Context::get_iterations(long long* it) {
   B200XF_CUDA(cudaMemcpyAsync(&iterations_host, iterations_dev, sizeof(long long), cudaMemcpyDeviceToHost, stream));
   B200XF_CUDA(cudaStreamSynchronize(stream));
   *it = iterations_host;
+  return 0;
+}
+
+int Context::enter() {
+  B200XF_CUDA(cudaSetDevice(device));
+  B200XF_CUDA(cudaEventRecord(ev_user, user_stream));
+  B200XF_CUDA(cudaStreamWaitEvent(stream, ev_user, 0));
+  return 0;
+}
+int Context::leave() {
+  B200XF_CUDA(cudaEventRecord(ev_own, stream));
+  B200XF_CUDA(cudaStreamWaitEvent(user_stream, ev_own, 0));
   return 0;
 }
 
@@ -442,6 +465,8 @@ int Context::join_side() {
   B200XF_CUDA(cudaEventRecord(ev_join, side_stream));
   B200XF_CUDA(cudaStreamWaitEvent(stream, ev_join, 0));
   side_dirty = false;
+  // everything the side stream has read is now ordered before whatever the compute stream does next
+  for (SideBuf* b : {&sb_dz, &sb_dzm, &sb_dq2, &sb_dh, &sb_dqkv}) b->pending[0] = b->pending[1] = false;
   return 0;
 }
 
@@ -771,14 +796,63 @@ int Context::loss_and_grad(int Nt, int workers_count, int write_grad) {
   return 0;
 }
 
+void Context::drop_graphs() {
+  for (auto& kv : graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  graphs.clear();
+}
+
 int Context::step_device(const long long* inp, const long long* target, int B, int S, int T1, int workers_count, int mode,
                          float* out6) {
   // mode 0: eval (fwd + loss), 1: fwd + bwd, 2: full train step
   if (T1 < 2) return set_error("target needs at least 2 positions");
-  const int T = T1 - 1;
-  B200XF_TRY(check_shapes(B, S, T));
+  B200XF_TRY(check_shapes(B, S, T1 - 1));
   if (workers_count <= 0) return set_error("workers_count must be positive");
   B200XF_CUDA(cudaSetDevice(device));
+  if (mode == 2 && use_graph && !phase_timing) {
+    // the graph reads the tokens from the context's own buffers
+    if (inp != tok_inp) B200XF_CUDA(cudaMemcpyAsync(tok_inp, inp, size_t(B) * S * sizeof(long long), cudaMemcpyDeviceToDevice, stream));
+    if (target != tok_target) B200XF_CUDA(cudaMemcpyAsync(tok_target, target, size_t(B) * T1 * sizeof(long long), cudaMemcpyDeviceToDevice, stream));
+    StepGraph& g = graphs[{B, S, T1, workers_count}];
+    if (!g.exec && ++g.seen > 2) {
+      if (graphs.size() > 64) { const StepGraph keep = g; drop_graphs(); graphs[{B, S, T1, workers_count}] = keep; }
+      StepGraph& gg = graphs[{B, S, T1, workers_count}];
+      cudaGraph_t graph = nullptr;
+      const long long launches_before = launches_total();
+      if (cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+        const int rc = step_body(tok_inp, tok_target, B, S, T1, workers_count, mode);
+        gg.launches = int(launches_total() - launches_before);  // kernels recorded into the graph
+        const cudaError_t e = cudaStreamEndCapture(stream, &graph);
+        if (rc == 0 && e == cudaSuccess && graph && cudaGraphInstantiate(&gg.exec, graph, 0) == cudaSuccess) {
+          cudaGraphDestroy(graph);
+        } else {
+          if (graph) cudaGraphDestroy(graph);
+          count_launch(-gg.launches);  // nothing was recorded after all
+          cudaGetLastError();       // capture is not possible here (e.g. a collective library that cannot be captured):
+          gg.exec = nullptr;        // stay on stream launches from now on
+          use_graph = false;
+        }
+      } else {
+        cudaGetLastError();
+        use_graph = false;
+      }
+    }
+    StepGraph& cur = graphs[{B, S, T1, workers_count}];
+    if (cur.exec) {
+      B200XF_CUDA(cudaGraphLaunch(cur.exec, stream));
+      if (cur.counted) count_launch(cur.launches); else cur.counted = true;  // the capture itself already counted them once
+      grads_clean = true;
+    } else {
+      B200XF_TRY(step_body(tok_inp, tok_target, B, S, T1, workers_count, mode));
+    }
+  } else {
+    B200XF_TRY(step_body(inp, target, B, S, T1, workers_count, mode));
+  }
+  if (out6) B200XF_CUDA(cudaMemcpyAsync(out6, metrics, 6 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  return 0;
+}
+
+int Context::step_body(const long long* inp, const long long* target, int B, int S, int T1, int workers_count, int mode) {
+  const int T = T1 - 1;
   B200XF_TRY(phase_mark(0));
   B200XF_TRY(prep_targets(target, tok_tgt_in, tok_labels, nonpad_count, B, T1, stream));
   B200XF_TRY(forward(inp, tok_tgt_in, B, S, T, nullptr, mode != 0));
@@ -811,7 +885,6 @@ int Context::step_device(const long long* inp, const long long* target, int B, i
     B200XF_CUDA(cudaMemcpyAsync(metrics + 3, metrics, 3 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
   }
   B200XF_TRY(phase_mark(4));
-  if (out6) B200XF_CUDA(cudaMemcpyAsync(out6, metrics, 6 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
   return 0;
 }
 

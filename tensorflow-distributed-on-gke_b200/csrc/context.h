@@ -25,7 +25,12 @@ void positional_encoding_host(float* out, int positions, int d);
 struct Context {
   b200xf_hparams hp{};
   int device = 0;
-  cudaStream_t stream = nullptr;
+  // All work runs on a stream the context owns (high priority, capturable); every entry point first makes it wait for
+  // the caller's stream and afterwards makes the caller's stream wait for it, so the caller sees ordinary stream order.
+  cudaStream_t stream = nullptr, user_stream = nullptr;
+  cudaEvent_t ev_user = nullptr, ev_own = nullptr;
+  int enter();
+  int leave();
 
   // ---- parameters (flat) and their logical views
   size_t total_params = 0;
@@ -113,6 +118,14 @@ struct Context {
   int section_done();
   int loss_and_grad(int Nt, int workers_count, int write_grad);
   int step_device(const long long* inp, const long long* target, int B, int S, int T1, int workers_count, int mode, float* out6);
+  int step_body(const long long* inp, const long long* target, int B, int S, int T1, int workers_count, int mode);
+  // A train step's ~330 launches and ~300 event operations cost about as much host time as the GPU needs to run them, so
+  // once a (B, S, T+1, workers) shape has been seen a few times the whole step is captured into a CUDA graph (PDL edges,
+  // side streams and NCCL included) and replayed.  B200XF_GRAPH=0 disables this.
+  struct StepGraph { cudaGraphExec_t exec = nullptr; int seen = 0; int launches = 0; bool counted = false; };
+  std::map<std::vector<int>, StepGraph> graphs;
+  bool use_graph = true;
+  void drop_graphs();
   int step_host(const long long* inp, const long long* target, int B, int S, int T1, int workers_count, float* out6_host);
 };
 
