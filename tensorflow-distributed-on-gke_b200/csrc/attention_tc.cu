@@ -64,7 +64,9 @@ __global__ void __launch_bounds__(kThreads, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                    const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do, const TcArgs p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // round up to 1024 B with pointer arithmetic (not an integer round trip) so the compiler keeps treating every
+  // access below as shared-memory (STS/LDS), not generic
+  uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sQ = smem; uint8_t* sK = sQ + kTileBytes; uint8_t* sV = sK + kTileBytes; uint8_t* sdO = sV + kTileBytes;
   uint8_t* sP = sdO + kTileBytes; uint8_t* sdS = sP + kPBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sdS + kPBytes);  // 0 load, 1 S/dP ready, 2 P/dS written, 3 outputs ready
@@ -220,7 +222,9 @@ __global__ void __launch_bounds__(kThreads, 2)
 attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                    const __grid_constant__ CUtensorMap tm_v, const TcArgs p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // round up to 1024 B with pointer arithmetic (not an integer round trip) so the compiler keeps treating every
+  // access below as shared-memory (STS/LDS), not generic
+  uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sQ = smem; uint8_t* sK = sQ + kTileBytes; uint8_t* sV = sK + kTileBytes; uint8_t* sP = sV + kTileBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kPBytes);  // 0 load, 1 S ready, 2 P written, 3 O ready
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);

@@ -111,7 +111,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             const __grid_constant__ CUtensorMap tmap_d, const GemmParams p) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // round up to 1024 B with pointer arithmetic (not an integer round trip) so the compiler keeps treating every
+  // access below as shared-memory (STS/LDS), not generic
+  uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* stage_base = smem + C::kStages * C::kStageBytes;  // 4 epilogue warps x 2 x 4 KB store staging
   float* sbias = reinterpret_cast<float*>(stage_base + 4 * 2 * 4096);  // [256] bias slice of the current tile
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(sbias + 256);
@@ -214,6 +216,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   } else {
     // ------------------------------------------------------------ epilogue (4 warps, 128 TMEM lanes)
     const int quarter = warp & 3;  // TMEM lane quarter this warp may touch
+    constexpr int kBiasPerThread = (BN + 127) / 128;
+    float bias_pre[kBiasPerThread];
+#pragma unroll
+    for (int k = 0; k < kBiasPerThread; ++k) {  // first tile's bias slice
+      const int j = int(threadIdx.x) - 64 + k * 128;
+      const int tn0 = (int(blockIdx.x) / p.tiles_m) % p.tiles_n;
+      bias_pre[k] = (p.bias != nullptr && int(blockIdx.x) < total_tiles && j < BN && tn0 * BN + j < p.N) ? __ldg(p.bias + tn0 * BN + j) : 0.f;
+    }
     int it = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
       const int tm = t % p.tiles_m, tn = (t / p.tiles_m) % p.tiles_n, z = t / (p.tiles_m * p.tiles_n);
@@ -227,8 +237,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const bool add_bias = p.bias != nullptr && z == 0;
       if (add_bias) {  // CTA-uniform: the four epilogue warps stage this tile's BN bias values once
         asm volatile("bar.sync 1, 128;" ::: "memory");   // everyone is done with the previous tile's slice
-        for (int j = threadIdx.x - 64; j < BN; j += 128) sbias[j] = (tn * BN + j < p.N) ? __ldg(p.bias + tn * BN + j) : 0.f;
+#pragma unroll
+        for (int k = 0; k < kBiasPerThread; ++k) { const int j = int(threadIdx.x) - 64 + k * 128; if (j < BN) sbias[j] = bias_pre[k]; }
         asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
+      if (p.bias != nullptr && t + int(gridDim.x) < total_tiles) {  // fetch the next tile's slice now; it is needed a whole tile later
+        const int tn_next = ((t + int(gridDim.x)) / p.tiles_m) % p.tiles_n;
+#pragma unroll
+        for (int k = 0; k < kBiasPerThread; ++k) {
+          const int j = int(threadIdx.x) - 64 + k * 128;
+          bias_pre[k] = (j < BN && tn_next * BN + j < p.N) ? __ldg(p.bias + tn_next * BN + j) : 0.f;
+        }
       }
       if (p.d_tma) {
         // TMEM -> registers -> 128B-swizzled staging tile (32 rows x 128 B per warp, double buffered) -> TMA store /
