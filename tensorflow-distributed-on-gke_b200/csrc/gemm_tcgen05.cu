@@ -31,7 +31,7 @@ namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;       // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int kThreads = 192;  // warp0 TMA, warp1 MMA, warps 2-5 epilogue
+constexpr int kThreads = 320;  // warp0 TMA, warp1 MMA, warps 2-9 epilogue (two per TMEM lane quarter, half the columns each)
 
 template <int BN>
 struct Cfg {
@@ -114,8 +114,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   // round up to 1024 B with pointer arithmetic (not an integer round trip) so the compiler keeps treating every
   // access below as shared-memory (STS/LDS), not generic
   uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
-  uint8_t* stage_base = smem + C::kStages * C::kStageBytes;  // 4 epilogue warps x 2 x 4 KB store staging
-  float* sbias = reinterpret_cast<float*>(stage_base + 4 * 2 * 4096);  // [256] bias slice of the current tile
+  uint8_t* stage_base = smem + C::kStages * C::kStageBytes;  // 8 epilogue warps x 4 KB store staging
+  float* sbias = reinterpret_cast<float*>(stage_base + 8 * 4096);  // [256] bias slice of the current tile
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(sbias + 256);
   uint64_t* empty_bar = full_bar + C::kStages;
   uint64_t* tmem_full = empty_bar + C::kStages;
@@ -131,7 +131,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     ptx::prefetch_tmap(&tmap_b);
     if (p.d_tma) ptx::prefetch_tmap(&tmap_d);
     for (int i = 0; i < C::kStages; ++i) { ptx::mbar_init(&full_bar[i], 1); ptx::mbar_init(&empty_bar[i], 1); }
-    for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tmem_full[i], 1); ptx::mbar_init(&tmem_empty[i], 4); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tmem_full[i], 1); ptx::mbar_init(&tmem_empty[i], 8); }
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -216,11 +216,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   } else {
     // ------------------------------------------------------------ epilogue (4 warps, 128 TMEM lanes)
     const int quarter = warp & 3;  // TMEM lane quarter this warp may touch
-    constexpr int kBiasPerThread = (BN + 127) / 128;
+    constexpr int kBiasPerThread = 1;  // 256 epilogue threads cover BN <= 256 columns
+    // this warp's share of the tile's 32-column chunks: the two warps of a lane quarter split the columns
+    const int halfsel = (warp - 2) >> 2;
+    constexpr int kChunksPerHalf = (BN / 32) / 2;
     float bias_pre[kBiasPerThread];
 #pragma unroll
     for (int k = 0; k < kBiasPerThread; ++k) {  // first tile's bias slice
-      const int j = int(threadIdx.x) - 64 + k * 128;
+      const int j = int(threadIdx.x) - 64 + k * 256;
       const int tn0 = (int(blockIdx.x) / p.tiles_m) % p.tiles_n;
       bias_pre[k] = (p.bias != nullptr && int(blockIdx.x) < total_tiles && j < BN && tn0 * BN + j < p.N) ? __ldg(p.bias + tn0 * BN + j) : 0.f;
     }
@@ -236,32 +239,31 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const uint32_t taddr = tmem_base + as * BN + (uint32_t(quarter * 32) << 16);
       const bool add_bias = p.bias != nullptr && z == 0;
       if (add_bias) {  // CTA-uniform: the four epilogue warps stage this tile's BN bias values once
-        asm volatile("bar.sync 1, 128;" ::: "memory");   // everyone is done with the previous tile's slice
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // everyone is done with the previous tile's slice
 #pragma unroll
-        for (int k = 0; k < kBiasPerThread; ++k) { const int j = int(threadIdx.x) - 64 + k * 128; if (j < BN) sbias[j] = bias_pre[k]; }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        for (int k = 0; k < kBiasPerThread; ++k) { const int j = int(threadIdx.x) - 64 + k * 256; if (j < BN) sbias[j] = bias_pre[k]; }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
       }
       if (p.bias != nullptr && t + int(gridDim.x) < total_tiles) {  // fetch the next tile's slice now; it is needed a whole tile later
         const int tn_next = ((t + int(gridDim.x)) / p.tiles_m) % p.tiles_n;
 #pragma unroll
         for (int k = 0; k < kBiasPerThread; ++k) {
-          const int j = int(threadIdx.x) - 64 + k * 128;
+          const int j = int(threadIdx.x) - 64 + k * 256;
           bias_pre[k] = (j < BN && tn_next * BN + j < p.N) ? __ldg(p.bias + tn_next * BN + j) : 0.f;
         }
       }
       if (p.d_tma) {
-        // TMEM -> registers -> 128B-swizzled staging tile (32 rows x 128 B per warp, double buffered) -> TMA store /
+        // TMEM -> registers -> 128B-swizzled staging tile (32 rows x 128 B, one per warp) -> TMA store /
         // TMA reduce-add: coalesced, asynchronous, clipped to the tensor bounds by the hardware.
-        constexpr int kColsPerBox = 32;  // fp32: 32 columns = 128 B per row; bf16 packs two 32-column chunks per box
-        const int chunks = p.d_fp32 ? 1 : 2;
-        uint8_t* my_stage = stage_base + (warp - 2) * 2 * 4096;
-        int sidx = 0;
+        const int chunks = p.d_fp32 ? 1 : 2;      // fp32: 32 columns = 128 B per row; bf16 packs two 32-column chunks per box
+        int c_begin = halfsel * kChunksPerHalf, c_end = c_begin + kChunksPerHalf;
+        if (kChunksPerHalf < chunks) { c_begin = halfsel ? BN / 32 : 0; c_end = BN / 32; }  // too narrow to split: first warp takes all
+        uint8_t* buf = stage_base + (warp - 2) * 4096;
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN / 32; c0 += chunks) {
+        for (int c0 = c_begin; c0 < c_end; c0 += chunks) {
           const int colbase = tn * BN + c0 * 32;
           if (colbase >= p.N) break;  // warp-uniform
-          uint8_t* buf = my_stage + sidx * 4096;
-          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");  // the store 2 boxes ago has read this buffer
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // the previous store has read the buffer
           __syncwarp();
           for (int cc = 0; cc < chunks; ++cc) {
             const int col0 = colbase + cc * 32;
@@ -293,12 +295,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             if (p.accumulate) ptx::tma_reduce_add_2d(&tmap_d, buf, colbase, r0); else ptx::tma_store_2d(&tmap_d, buf, colbase, r0);
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
-          sidx ^= 1;
         }
-        (void)kColsPerBox;
       } else {
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = (kChunksPerHalf ? halfsel * kChunksPerHalf : (halfsel ? BN / 32 : 0)); c < (kChunksPerHalf ? (halfsel + 1) * kChunksPerHalf : BN / 32); ++c) {
         const int col0 = tn * BN + c * 32;
         if (col0 >= p.N) break;  // warp-uniform
         uint32_t v[32];
