@@ -30,7 +30,7 @@ UNIT = "tokens/s"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--config", default="base", choices=["tutorial", "base", "big", "long"])
     ap.add_argument("--impl", default="b200xf", choices=["b200xf", "reference"])
