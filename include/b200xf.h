@@ -142,14 +142,17 @@ int b200xf_debug_gemm_trace(void* device_u64_buffer);
 
 /* scaled_dot_product_attention + masks + split/merge heads (transformer_model.py:56-70,73-109,124-131,160-163).
  * q [B*Sq, ldq], k/v [B*Sk, ld*], o [B*Sq, ldo] bf16, head h in columns [h*dk,(h+1)*dk); key_tokens [B,Sk] int64;
- * lse fp32 [B,H,Sq,2] = {row max, log2(row sum)} of the scaled, masked scores in the log2 domain. */
+ * lse fp32 [B,H,Sq,2] = {row max, log2(row sum)} of the scaled, masked scores in the log2 domain.
+ * Backward scratch: delta_scratch fp32 [B,H,Sq]; dq_acc_scratch fp32 [B*Sq, H*dk] or NULL — with it, head size 64 and
+ * sequences longer than one 128-key tile run the tcgen05 multi-tile backward (dQ accumulated by TMA reduce-add), without
+ * it the mma.sync kernels. */
 int b200xf_attention_fwd(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, void* o, int ldo,
                          float* lse, const int64_t* key_tokens, int causal, int B, int H, int Sq, int Sk, int dk,
                          void* stream);
 int b200xf_attention_bwd(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, const void* o, int ldo,
                          const float* lse, const int64_t* key_tokens, int causal, int B, int H, int Sq, int Sk, int dk,
                          const void* d_o, int lddo, void* dq, int lddq, void* dk_out, int lddk, void* dv_out, int lddv,
-                         float* delta_scratch, void* stream);
+                         float* delta_scratch, float* dq_acc_scratch, void* stream);
 
 /* LayerNormalization(epsilon) of (x + resid) (transformer_model.py:187-188,198,204).  bf16 rows of length d.
  * z_out (optional) receives x+resid; mean/rstd fp32 [rows]. */

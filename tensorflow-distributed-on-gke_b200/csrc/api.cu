@@ -163,14 +163,15 @@ int b200xf_attention_fwd(const void* q, int ldq, const void* k, int ldk, const v
 }
 int b200xf_attention_bwd(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, const void* o, int ldo, const float* lse,
                          const int64_t* key_tokens, int causal, int B, int H, int Sq, int Sk, int dk, const void* d_o, int lddo,
-                         void* dq, int lddq, void* dk_out, int lddk, void* dv_out, int lddv, float* delta_scratch, void* stream) {
+                         void* dq, int lddq, void* dk_out, int lddk, void* dv_out, int lddv, float* delta_scratch, float* dq_acc_scratch,
+                         void* stream) {
   AttnArgs a;
   a.q = static_cast<const bf16*>(q); a.ldq = ldq; a.k = static_cast<const bf16*>(k); a.ldk = ldk; a.v = static_cast<const bf16*>(v); a.ldv = ldv;
   a.o = const_cast<bf16*>(static_cast<const bf16*>(o)); a.ldo = ldo; a.lse = const_cast<float*>(lse);
   a.key_tokens = reinterpret_cast<const long long*>(key_tokens); a.causal = causal;
   a.B = B; a.H = H; a.Sq = Sq; a.Sk = Sk; a.dk = dk;
   a.d_o = static_cast<const bf16*>(d_o); a.lddo = lddo; a.dq = static_cast<bf16*>(dq); a.lddq = lddq;
-  a.dk_out = static_cast<bf16*>(dk_out); a.lddk = lddk; a.dv_out = static_cast<bf16*>(dv_out); a.lddv = lddv; a.delta = delta_scratch;
+  a.dk_out = static_cast<bf16*>(dk_out); a.lddk = lddk; a.dv_out = static_cast<bf16*>(dv_out); a.lddv = lddv; a.delta = delta_scratch; a.dq_acc = dq_acc_scratch;
   return attention_bwd(a, static_cast<cudaStream_t>(stream));
 }
 

@@ -498,6 +498,7 @@ int attention_fwd(const AttnArgs& a, cudaStream_t stream) {
 int attention_bwd(const AttnArgs& a, cudaStream_t stream) {
   B200XF_TRY(check(a, true));
   if (attention_tc_supported(a)) return attention_bwd_tc(a, stream);
+  if (attention_tc_multi_supported(a)) return attention_bwd_tc_multi(a, stream);
   const KernelArgs p = pack(a);
   const dim3 gq((a.Sq + kTile - 1) / kTile, a.H, a.B), gk((a.Sk + kTile - 1) / kTile, a.H, a.B);
   switch (a.dk) {

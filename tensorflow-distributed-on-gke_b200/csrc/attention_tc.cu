@@ -11,6 +11,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <mutex>
 
 #include "internal.h"
@@ -330,7 +331,287 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
   if (warp == 1) { ptx::tc_fence_after(); ptx::tmem_dealloc(tmem, 256); }
 }
 
+// ---------------------------------------------------------------------------------------------------------- backward, any length
+// One CTA per (128-key tile, head, batch) walks the 128-query tiles that can see those keys.  Per (q tile, kv tile) pair:
+//   S = Q K^T, dP = dO V^T -> threads: P = exp2(s - m_i - log2 l_i), dS = P (dP - delta_i) -> smem ->
+//   dV += P^T dO, dK += dS^T Q (accumulated in TMEM over the q tiles), dQ_pair = dS K -> fp32 staging -> TMA reduce-add
+//   into an fp32 dQ accumulator (other kv tiles add their share).  delta_i = rowsum(dO * O) and the zeroing of the
+//   accumulator come from attn_bwd_prep_kernel; attn_bwd_dq_out_kernel scales and rounds dQ at the end.
+constexpr int kSmemBwdMulti = 2 * kTileBytes /*K V*/ + 4 * kTileBytes /*Q dO x2*/ + 2 * kPBytes /*P dS*/ + 2 * kTileBytes /*dQ fp32 staging*/ +
+                              1024 /*alignment*/ + 4096 /*barriers, stats, mask*/;
+
+struct TcMultiArgs {
+  const long long* key_tokens;
+  const float* lse; const float* delta;   // [B,H,Sq,2], [B,H,Sq]
+  bf16 *dk_out, *dv_out; int lddk, lddv;
+  int H, Sq, Sk, causal;
+  float scale, scale_log2;
+};
+
+constexpr int kThreadsMulti = 320;  // warp 0: TMA + MMA issue, warp 1: TMEM allocation, warps 2-9: two threads per row (64 keys each)
+
+__global__ void __launch_bounds__(kThreadsMulti, 1)
+attn_bwd_tc_multi_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                         const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do,
+                         const __grid_constant__ CUtensorMap tm_dq, const TcMultiArgs p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sK = smem; uint8_t* sV = sK + kTileBytes;
+  uint8_t* sQ = sV + kTileBytes;            // [2] stages
+  uint8_t* sdO = sQ + 2 * kTileBytes;       // [2] stages
+  uint8_t* sP = sdO + 2 * kTileBytes; uint8_t* sdS = sP + kPBytes;
+  uint8_t* sdQ = sdS + kPBytes;             // two [128 rows][32 fp32] boxes
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sdQ + 2 * kTileBytes);
+  uint64_t* bar_kv = bars; uint64_t* q_full = bars + 1; uint64_t* q_empty = bars + 3;
+  uint64_t* s_ready = bars + 5; uint64_t* p_ready = bars + 6; uint64_t* dq_ready = bars + 7;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  int* s_mask = reinterpret_cast<int*>(bars + 10);   // [128]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int jt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int k0 = jt * kT;
+  const long long* toks = p.key_tokens + size_t(b) * p.Sk;
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tm_q); ptx::prefetch_tmap(&tm_k); ptx::prefetch_tmap(&tm_v); ptx::prefetch_tmap(&tm_do); ptx::prefetch_tmap(&tm_dq);
+    ptx::mbar_init(bar_kv, 1);
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(&q_full[i], 1); ptx::mbar_init(&q_empty[i], 1); }
+    ptx::mbar_init(s_ready, 1); ptx::mbar_init(p_ready, 256); ptx::mbar_init(dq_ready, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) { ptx::tmem_alloc(tmem_slot, 512); ptx::tmem_relinquish(); }
+  pdl_wait();
+  pdl_trigger();
+  if (warp >= 2 && warp < 6) {
+    const int j = threadIdx.x - 64;
+    s_mask[j] = (k0 + j >= p.Sk) ? 2 : (toks[k0 + j] == 0 ? 1 : 0);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tdP = tmem + 128, tdQ = tmem + 256, tdK = tmem + 320, tdV = tmem + 384;
+
+  // query tiles that can see this key tile: all of them, except under a causal mask whose rows cannot be fully masked
+  const int nq = (p.Sq + kT - 1) / kT;
+  const int i_begin = (p.causal && toks[0] != 0) ? jt : 0;
+  const int npairs = nq - i_begin;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const uint32_t aK = ptx::smem_u32(sK), aV = ptx::smem_u32(sV), aP = ptx::smem_u32(sP), aDS = ptx::smem_u32(sdS);
+      constexpr uint32_t idesc_kk = ptx::make_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t idesc_mm = ptx::make_idesc_bf16(128, 64, 1, 1);
+      constexpr uint32_t idesc_km = ptx::make_idesc_bf16(128, 64, 0, 1);
+      auto load_q = [&](int it) {
+        const int st = it & 1, q0 = (i_begin + it) * kT;
+        ptx::mbar_expect_tx(&q_full[st], 2 * kTileBytes);
+        ptx::tma_load_2d(sQ + st * kTileBytes, &tm_q, &q_full[st], h * kD, b * p.Sq + q0);
+        ptx::tma_load_2d(sdO + st * kTileBytes, &tm_do, &q_full[st], h * kD, b * p.Sq + q0);
+      };
+      ptx::mbar_expect_tx(bar_kv, 2 * kTileBytes);
+      ptx::tma_load_2d(sK, &tm_k, bar_kv, h * kD, b * p.Sk + k0);
+      ptx::tma_load_2d(sV, &tm_v, bar_kv, h * kD, b * p.Sk + k0);
+      if (npairs > 0) load_q(0);
+      ptx::mbar_wait(bar_kv, 0);
+      for (int it = 0; it < npairs; ++it) {
+        const int st = it & 1;
+        const uint32_t aQ = ptx::smem_u32(sQ + st * kTileBytes), aDO = ptx::smem_u32(sdO + st * kTileBytes);
+        ptx::mbar_wait(&q_full[st], (it >> 1) & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          ptx::umma_bf16(tS, ptx::make_smem_desc(aQ + k * 32, 16, 1024), ptx::make_smem_desc(aK + k * 32, 16, 1024), idesc_kk, k > 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          ptx::umma_bf16(tdP, ptx::make_smem_desc(aDO + k * 32, 16, 1024), ptx::make_smem_desc(aV + k * 32, 16, 1024), idesc_kk, k > 0);
+        ptx::umma_commit(s_ready);
+        if (it + 1 < npairs) {  // prefetch the next query tile while this pair is being processed
+          ptx::mbar_wait(&q_empty[(it + 1) & 1], (((it + 1) >> 1) & 1) ^ 1);
+          load_q(it + 1);
+        }
+        ptx::mbar_wait(p_ready, it & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          ptx::umma_bf16(tdV, ptx::make_smem_desc(aP + k * 2048, kTileBytes, 1024), ptx::make_smem_desc(aDO + k * 2048, kTileBytes, 1024), idesc_mm, (it > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          ptx::umma_bf16(tdK, ptx::make_smem_desc(aDS + k * 2048, kTileBytes, 1024), ptx::make_smem_desc(aQ + k * 2048, kTileBytes, 1024), idesc_mm, (it > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          ptx::umma_bf16(tdQ, ptx::make_smem_desc(aDS + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
+                         ptx::make_smem_desc(aK + k * 2048, kTileBytes, 1024), idesc_km, k > 0);
+        ptx::umma_commit(dq_ready);
+      }
+    }
+  } else if (warp >= 2) {
+    const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;              // which 64 of the tile's 128 key columns (32 of the 64 output columns) this thread handles
+    const int i = quarter * 32 + lane;             // row of this thread: a query row in the pair loop, a key row at the end
+    const uint32_t lane_base = uint32_t(quarter * 32) << 16;
+    const size_t stat_base = (size_t(b) * p.H + h) * p.Sq;
+    auto load_stats = [&](int it, float& m, float& l2, float& dl) {
+      const int row = (i_begin + it) * kT + i;
+      if (it < npairs && row < p.Sq) {
+        const float2 ml = reinterpret_cast<const float2*>(p.lse)[stat_base + row];
+        m = ml.x; l2 = ml.y; dl = p.delta[stat_base + row];
+      } else { m = INFINITY; l2 = 0.f; dl = 0.f; }   // exp2(x - inf) = 0: rows past the sequence contribute nothing
+    };
+    float m_cur, l_cur, d_cur;
+    load_stats(0, m_cur, l_cur, d_cur);
+    for (int it = 0; it < npairs; ++it) {
+      const int q0 = (i_begin + it) * kT;
+      float m_nxt, l_nxt, d_nxt;
+      load_stats(it + 1, m_nxt, l_nxt, d_nxt);   // in flight during this pair
+      ptx::mbar_wait(s_ready, it & 1);
+      ptx::tc_fence_after();
+#pragma unroll
+      for (int c = half * 2; c < half * 2 + 2; ++c) {
+        float sv[32], dp[32];
+        tmem_ld32(tS + lane_base + c * 32, sv);
+        tmem_ld32(tdP + lane_base + c * 32, dp);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int key = c * 32 + j;
+          const int mk = s_mask[key];
+          float v = sv[j] * p.scale_log2;
+          if (mk == 1 || (p.causal && k0 + key > q0 + i)) v = kMasked;
+          const float pr = (mk == 2) ? 0.f : exp2f((v - m_cur) - l_cur);
+          sv[j] = pr;
+          dp[j] = pr * (dp[j] - d_cur);
+        }
+        store_row32(sP, i, c * 32, sv);
+        store_row32(sdS, i, c * 32, dp);
+      }
+      ptx::tc_fence_before();
+      ptx::fence_proxy_async();
+      ptx::mbar_arrive(p_ready);
+
+      ptx::mbar_wait(dq_ready, it & 1);
+      ptx::tc_fence_after();
+      if (threadIdx.x == 64) {
+        ptx::mbar_arrive(&q_empty[it & 1]);  // every MMA that read this Q / dO stage has completed
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // the previous pair's reduce-add has read the staging tile
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      {   // this pair's share of dQ row i -> fp32 staging (two 128B-swizzled [128][32] boxes, one per column half)
+        const int c = half;
+        float f[32];
+        tmem_ld32(tdQ + lane_base + c * 32, f);
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          *reinterpret_cast<float4*>(sdQ + c * kTileBytes + i * 128 + ((q ^ (i & 7)) << 4)) =
+              make_float4(f[q * 4] * p.scale, f[q * 4 + 1] * p.scale, f[q * 4 + 2] * p.scale, f[q * 4 + 3] * p.scale);
+      }
+      ptx::tc_fence_before();
+      ptx::fence_proxy_async();
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (threadIdx.x == 64) {
+        ptx::tma_reduce_add_2d(&tm_dq, sdQ, h * kD, b * p.Sq + q0);
+        ptx::tma_reduce_add_2d(&tm_dq, sdQ + kTileBytes, h * kD + 32, b * p.Sq + q0);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+      m_cur = m_nxt; l_cur = l_nxt; d_cur = d_nxt;
+    }
+    if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    // dK, dV rows of this key tile (zero when no query tile was visited)
+    const bool key_ok = k0 + i < p.Sk;
+    bf16* dstk = p.dk_out + (size_t(b) * p.Sk + (key_ok ? k0 + i : 0)) * p.lddk + h * kD;
+    bf16* dstv = p.dv_out + (size_t(b) * p.Sk + (key_ok ? k0 + i : 0)) * p.lddv + h * kD;
+    {
+      const int c = half;
+      float fk[32], fv[32];
+      if (npairs > 0) { tmem_ld32(tdK + lane_base + c * 32, fk); tmem_ld32(tdV + lane_base + c * 32, fv); }
+      else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { fk[j] = 0.f; fv[j] = 0.f; }
+      }
+      if (key_ok) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 u, w;
+          u.x = ptx::pack_bf16x2(fk[q * 8] * p.scale, fk[q * 8 + 1] * p.scale); u.y = ptx::pack_bf16x2(fk[q * 8 + 2] * p.scale, fk[q * 8 + 3] * p.scale);
+          u.z = ptx::pack_bf16x2(fk[q * 8 + 4] * p.scale, fk[q * 8 + 5] * p.scale); u.w = ptx::pack_bf16x2(fk[q * 8 + 6] * p.scale, fk[q * 8 + 7] * p.scale);
+          w.x = ptx::pack_bf16x2(fv[q * 8], fv[q * 8 + 1]); w.y = ptx::pack_bf16x2(fv[q * 8 + 2], fv[q * 8 + 3]);
+          w.z = ptx::pack_bf16x2(fv[q * 8 + 4], fv[q * 8 + 5]); w.w = ptx::pack_bf16x2(fv[q * 8 + 6], fv[q * 8 + 7]);
+          *reinterpret_cast<uint4*>(dstk + c * 32 + q * 8) = u;
+          *reinterpret_cast<uint4*>(dstv + c * 32 + q * 8) = w;
+        }
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { ptx::tc_fence_after(); ptx::tmem_dealloc(tmem, 512); }
+}
+
+// delta[b,h,i] = sum_c dO[i,c] * O[i,c]; also clears the fp32 dQ accumulator.  One warp per (row, head).
+__global__ void __launch_bounds__(256)
+attn_bwd_prep_kernel(const bf16* __restrict__ o, int ldo, const bf16* __restrict__ d_o, int lddo, float* __restrict__ delta,
+                     float* __restrict__ dq_acc, int H, int Sq, int total_rows) {
+  pdl_wait();
+  pdl_trigger();
+  const int lane = threadIdx.x & 31;
+  const int idx = blockIdx.x * 8 + (threadIdx.x >> 5);   // (row, head) pair
+  if (idx >= total_rows * H) return;
+  const int row = idx / H, h = idx % H;
+  const uint32_t uo = *reinterpret_cast<const uint32_t*>(o + size_t(row) * ldo + h * kD + lane * 2);
+  const uint32_t ud = *reinterpret_cast<const uint32_t*>(d_o + size_t(row) * lddo + h * kD + lane * 2);
+  float acc = ptx::bf16_lo(uo) * ptx::bf16_lo(ud) + ptx::bf16_hi(uo) * ptx::bf16_hi(ud);
+#pragma unroll
+  for (int s2 = 16; s2 > 0; s2 >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s2);
+  const int b = row / Sq, i = row % Sq;
+  if (lane == 0) delta[(size_t(b) * H + h) * Sq + i] = acc;
+  *reinterpret_cast<float2*>(dq_acc + (size_t(row) * H + h) * kD + lane * 2) = make_float2(0.f, 0.f);
+}
+
+__global__ void __launch_bounds__(256)
+attn_bwd_dq_out_kernel(const float* __restrict__ dq_acc, bf16* __restrict__ dq, int lddq, int cols, size_t total) {
+  pdl_wait();
+  pdl_trigger();
+  for (size_t e = (blockIdx.x * size_t(blockDim.x) + threadIdx.x) * 4; e < total; e += size_t(gridDim.x) * blockDim.x * 4) {
+    const size_t row = e / cols; const int c = int(e % cols);
+    const float4 f = *reinterpret_cast<const float4*>(dq_acc + e);
+    uint2 u; u.x = ptx::pack_bf16x2(f.x, f.y); u.y = ptx::pack_bf16x2(f.z, f.w);
+    *reinterpret_cast<uint2*>(dq + row * lddq + c) = u;
+  }
+}
+
 }  // namespace
+
+bool attention_tc_multi_supported(const AttnArgs& a) {
+  static int enabled = -1;
+  if (enabled < 0) { const char* e = getenv("B200XF_ATTENTION_TC"); enabled = (e && atoi(e) == 0) ? 0 : 1; }
+  return enabled && a.dk == kD && a.dq_acc != nullptr && a.Sq > 0 && a.Sk > 0;
+}
+
+int attention_bwd_tc_multi(const AttnArgs& a, cudaStream_t stream) {
+  CUtensorMap tq, tk, tv, tdo, tdq;
+  const uint64_t cols = uint64_t(a.H) * kD;
+  B200XF_TRY(tensor_map_2d(a.q, cols, uint64_t(a.B) * a.Sq, a.ldq, kT, &tq, 0));
+  B200XF_TRY(tensor_map_2d(a.k, cols, uint64_t(a.B) * a.Sk, a.ldk, kT, &tk, 0));
+  B200XF_TRY(tensor_map_2d(a.v, cols, uint64_t(a.B) * a.Sk, a.ldv, kT, &tv, 0));
+  B200XF_TRY(tensor_map_2d(a.d_o, cols, uint64_t(a.B) * a.Sq, a.lddo, kT, &tdo, 0));
+  B200XF_TRY(tensor_map_2d(a.dq_acc, cols, uint64_t(a.B) * a.Sq, cols, kT, &tdq, 1));
+  const int rows = a.B * a.Sq;
+  B200XF_CUDA(launch_k(attn_bwd_prep_kernel, (rows * a.H + 7) / 8, 256, 0, stream, static_cast<const bf16*>(a.o), a.ldo, a.d_o, a.lddo,
+                       a.delta, a.dq_acc, a.H, a.Sq, rows));
+  TcMultiArgs p{};
+  p.key_tokens = a.key_tokens; p.lse = a.lse; p.delta = a.delta;
+  p.dk_out = a.dk_out; p.dv_out = a.dv_out; p.lddk = a.lddk; p.lddv = a.lddv;
+  p.H = a.H; p.Sq = a.Sq; p.Sk = a.Sk; p.causal = a.causal;
+  p.scale = 1.0f / sqrtf(float(a.dk)); p.scale_log2 = p.scale * kLog2e;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] { attr_err = cudaFuncSetAttribute(attn_bwd_tc_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBwdMulti); });
+  if (attr_err != cudaSuccess) return set_error("cudaFuncSetAttribute(attn_bwd_tc_multi): %s", cudaGetErrorString(attr_err));
+  B200XF_CUDA(launch_k(attn_bwd_tc_multi_kernel, dim3((a.Sk + kT - 1) / kT, a.H, a.B), kThreadsMulti, kSmemBwdMulti, stream, tq, tk, tv, tdo, tdq, p));
+  const size_t total = size_t(rows) * cols;
+  B200XF_CUDA(launch_k(attn_bwd_dq_out_kernel, int(std::min<size_t>((total / 4 + 255) / 256, 4096)), 256, 0, stream,
+                       static_cast<const float*>(a.dq_acc), a.dq, a.lddq, int(cols), total));
+  count_launch(3);
+  return 0;
+}
 
 bool attention_tc_supported(const AttnArgs& a) {
   static int enabled = -1;

@@ -269,7 +269,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   need(N * size_t(vt_ld), 2);                                       // logits / dlogits
   for (int i = 0; i < 9; ++i) need(nd, 2);                          // dA dB dctx, 2 x (dz dzm dq2)
   need(2 * nff, 2); need(2 * 3 * nd, 2);                            // 2 x dh, 2 x dqkv
-  need(N * H, 4);                                                   // delta
+  need(N * H, 4); need(nd, 4);                                      // delta, fp32 dQ accumulator
   for (int i = 0; i < 4; ++i) need(N + 64, 8);                      // inp, target, tgt_in, labels
   need(N, 4); need(N, 4);                                           // row_loss, row_correct
   need(red_capacity, 4); need(emb_scratch_bytes, 1);
@@ -307,7 +307,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
     for (SideBuf* b : {&sb_dz, &sb_dzm, &sb_dq2, &sb_dh, &sb_dqkv}) B200XF_CUDA(cudaEventCreateWithFlags(&b->done[c], cudaEventDisableTiming));
   }
   dz = sb_dz.buf[0]; dzm = sb_dzm.buf[0]; dq2 = sb_dq2.buf[0]; dh = sb_dh.buf[0]; dqkv = sb_dqkv.buf[0];
-  B200XF_TRY(arena_alloc(&delta, N * H));
+  B200XF_TRY(arena_alloc(&delta, N * H)); B200XF_TRY(arena_alloc(&dq_acc, nd));
   B200XF_TRY(arena_alloc(&tok_inp, N + 64)); B200XF_TRY(arena_alloc(&tok_target, N + 64));
   B200XF_TRY(arena_alloc(&tok_tgt_in, N + 64)); B200XF_TRY(arena_alloc(&tok_labels, N + 64));
   B200XF_TRY(arena_alloc(&row_loss, N)); B200XF_TRY(arena_alloc(&row_correct, N));
@@ -685,7 +685,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     c2.B = B; c2.H = H; c2.Sq = T; c2.Sk = S; c2.dk = dk;
     B200XF_TRY(sb_write(sb_dq2, &dq2));
     c2.d_o = dctx; c2.lddo = d; c2.dq = dq2; c2.lddq = d;
-    c2.dk_out = dkv + size_t(l) * 2 * d; c2.dv_out = dkv + size_t(l) * 2 * d + d; c2.lddk = c2.lddv = kv_all.ld; c2.delta = delta;
+    c2.dk_out = dkv + size_t(l) * 2 * d; c2.dv_out = dkv + size_t(l) * 2 * d + d; c2.lddk = c2.lddv = kv_all.ld; c2.delta = delta; c2.dq_acc = dq_acc;
     B200XF_TRY(attention_bwd(c2, stream));
     B200XF_TRY(colsum(dq2, d, Nt, d, w.q2.b));
     B200XF_TRY(dense_wgrad(a.o1, dq2, Nt, w.q2));
@@ -701,7 +701,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     s1.B = B; s1.H = H; s1.Sq = T; s1.Sk = T; s1.dk = dk;
     B200XF_TRY(sb_write(sb_dqkv, &dqkv));
     s1.d_o = dctx; s1.lddo = d; s1.dq = dqkv; s1.dk_out = dqkv + d; s1.dv_out = dqkv + 2 * d; s1.lddq = s1.lddk = s1.lddv = 3 * d;
-    s1.delta = delta;
+    s1.delta = delta; s1.dq_acc = dq_acc;
     B200XF_TRY(attention_bwd(s1, stream));
     B200XF_TRY(colsum(dqkv, 3 * d, Nt, 3 * d, w.qkv1.b));
     B200XF_TRY(dense_wgrad(x, dqkv, Nt, w.qkv1));
@@ -737,7 +737,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     at.B = B; at.H = H; at.Sq = S; at.Sk = S; at.dk = dk;
     B200XF_TRY(sb_write(sb_dqkv, &dqkv));
     at.d_o = dctx; at.lddo = d; at.dq = dqkv; at.dk_out = dqkv + d; at.dv_out = dqkv + 2 * d; at.lddq = at.lddk = at.lddv = 3 * d;
-    at.delta = delta;
+    at.delta = delta; at.dq_acc = dq_acc;
     B200XF_TRY(attention_bwd(at, stream));
     B200XF_TRY(colsum(dqkv, 3 * d, Ns, 3 * d, w.qkv.b));
     B200XF_TRY(dense_wgrad(x, dqkv, Ns, w.qkv));

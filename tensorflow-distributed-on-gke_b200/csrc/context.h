@@ -71,7 +71,7 @@ struct Context {
   bool dropout_on = false; unsigned long long dropout_seed = 0x5EEDull;
   bf16 *dzm = nullptr, *dsub = nullptr;
   bf16 *dA = nullptr, *dB = nullptr, *dz = nullptr, *dctx = nullptr, *dq2 = nullptr, *dh = nullptr, *dqkv = nullptr;
-  float *delta = nullptr, *row_loss = nullptr, *red_scratch = nullptr, *pe_in = nullptr, *pe_tgt = nullptr, *metrics = nullptr;
+  float *dq_acc = nullptr, *delta = nullptr, *row_loss = nullptr, *red_scratch = nullptr, *pe_in = nullptr, *pe_tgt = nullptr, *metrics = nullptr;
   int *row_correct = nullptr, *nonpad_count = nullptr;
   size_t red_capacity = 0, red_used = 0;
   std::vector<ReduceJob> red_jobs;

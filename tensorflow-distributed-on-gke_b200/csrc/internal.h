@@ -84,7 +84,7 @@ struct AttnArgs {
   bf16* dk_out = nullptr; int lddk = 0;
   bf16* dv_out = nullptr; int lddv = 0;
   float* delta = nullptr;                 // scratch [B,H,Sq]
-  float* probs = nullptr;                 // optional fwd output [B,H,Sq,Sk] fp32 (inference API only)
+  float* dq_acc = nullptr;                // optional scratch: fp32 [B*Sq, H*dk] dQ accumulator (enables the multi-tile tcgen05 backward)
 };
 int attention_fwd(const AttnArgs& a, cudaStream_t stream);
 int attention_bwd(const AttnArgs& a, cudaStream_t stream);
@@ -94,6 +94,9 @@ int attention_probs(const AttnArgs& a, float* out, cudaStream_t stream);
 bool attention_tc_supported(const AttnArgs& a);
 int attention_fwd_tc(const AttnArgs& a, cudaStream_t stream);
 int attention_bwd_tc(const AttnArgs& a, cudaStream_t stream);
+// tcgen05 multi-tile backward (any Sq, Sk; head size 64; needs AttnArgs::dq_acc)
+bool attention_tc_multi_supported(const AttnArgs& a);
+int attention_bwd_tc_multi(const AttnArgs& a, cudaStream_t stream);
 
 // ---- LayerNorm (+ optional residual add) fwd / bwd (transformer_model.py:187-188,198,204)
 int layernorm_fwd(const bf16* x, const bf16* resid, const float* gamma, const float* beta, bf16* y, bf16* z_out,

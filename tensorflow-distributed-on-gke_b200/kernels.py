@@ -55,7 +55,7 @@ def attention_fwd(q, k, v, key_tokens, causal, H):
     return o, lse
 
 
-def attention_bwd(q, k, v, o, lse, d_o, key_tokens, causal, H):
+def attention_bwd(q, k, v, o, lse, d_o, key_tokens, causal, H, dq_scratch=True):
     _need_cuda(q, k, v, o, d_o)
     lib = _lib.load()
     B, Sq, D = q.shape
@@ -65,9 +65,10 @@ def attention_bwd(q, k, v, o, lse, d_o, key_tokens, causal, H):
     dkk = torch.empty((B, Sk, D), device=q.device, dtype=torch.bfloat16)
     dv = torch.empty((B, Sk, D), device=q.device, dtype=torch.bfloat16)
     delta = torch.empty((B, H, Sq), device=q.device, dtype=torch.float32)
+    dq_acc = torch.empty((B * Sq, D), device=q.device, dtype=torch.float32) if dq_scratch else None
     check(lib.b200xf_attention_bwd(ptr(q), q.stride(1), ptr(k), k.stride(1), ptr(v), v.stride(1), ptr(o), o.stride(1), ptr(lse),
                                    ptr(key_tokens), int(causal), B, H, Sq, Sk, dk, ptr(d_o), d_o.stride(1), ptr(dq), dq.stride(1),
-                                   ptr(dkk), dkk.stride(1), ptr(dv), dv.stride(1), ptr(delta), stream_ptr()))
+                                   ptr(dkk), dkk.stride(1), ptr(dv), dv.stride(1), ptr(delta), ptr(dq_acc), stream_ptr()))
     return dq, dkk, dv
 
 

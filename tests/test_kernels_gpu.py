@@ -111,6 +111,9 @@ ATTN_CASES = [  # B, H, Sq, Sk, dk, causal, pad_first_token
     # single-tile tcgen05 backward (Sq, Sk <= 128, dk 64): ragged tile, cross shapes, fully masked causal rows
     (3, 4, 100, 100, 64, True, False), (2, 8, 128, 77, 64, False, False), (2, 4, 40, 128, 64, False, False),
     (2, 2, 128, 128, 64, True, True), (5, 3, 17, 9, 64, False, False),
+    # multi-tile tcgen05 backward (head size 64, longer than one tile): ragged tails, cross shapes, causal skipping, masked rows
+    (2, 4, 256, 256, 64, True, False), (1, 2, 300, 300, 64, False, False), (2, 2, 200, 450, 64, False, False),
+    (1, 2, 384, 130, 64, False, False), (2, 2, 257, 257, 64, True, True), (1, 8, 1024, 1024, 64, True, False),
 ]
 
 
@@ -138,12 +141,13 @@ def test_attention_fwd_bwd(case):
     err = float((o.float() - ref.detach()).abs().max())
     assert err < 2e-2, f"{case}: fwd max abs err {err}"  # bf16 probabilities and output
     d_o = _bf(torch.randn(B, Sq, D, device=DEV, generator=g))
-    dq, dk_, dv = K.attention_bwd(q, k, v, o, lse, d_o, toks, causal, H)
     ref.backward(d_o.float())
-    for name, got, want in (("dq", dq, qr.grad), ("dk", dk_, kr.grad), ("dv", dv, vr.grad)):
-        assert torch.isfinite(got.float()).all(), f"{case}: {name} not finite"
-        e = _rel(got, want)
-        assert e < 2e-2, f"{case}: {name} rel err {e}"
+    for scratch in (True, False):  # with the fp32 dQ accumulator (tcgen05 paths) and without it (mma.sync path for long sequences)
+        dq, dk_, dv = K.attention_bwd(q, k, v, o, lse, d_o, toks, causal, H, dq_scratch=scratch)
+        for name, got, want in (("dq", dq, qr.grad), ("dk", dk_, kr.grad), ("dv", dv, vr.grad)):
+            assert torch.isfinite(got.float()).all(), f"{case}: {name} not finite"
+            e = _rel(got, want)
+            assert e < 2e-2, f"{case} scratch={scratch}: {name} rel err {e}"
 
 
 # ------------------------------------------------------------------------------------------ LayerNorm
