@@ -331,6 +331,166 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
   if (warp == 1) { ptx::tc_fence_after(); ptx::tmem_dealloc(tmem, 256); }
 }
 
+constexpr int kThreadsMulti = 320;  // warp 0: TMA + MMA issue, warp 1: TMEM allocation, warps 2-9: two threads per row (64 keys each)
+
+// ---------------------------------------------------------------------------------------------------------- forward, any length
+// One CTA per (128-query tile, head, batch) walks the 128-key tiles (TMA double buffered).  Per tile: S = Q K^T (TMEM) ->
+// two threads per query row (64 keys each) mask / online-softmax it, exchange their partial max and sum through shared
+// memory, write P (bf16) -> O_tile = P V (TMEM) -> each thread folds its 32 output columns into a register accumulator
+// with the usual exp2(m_old - m_new) correction.
+constexpr int kSmemFwdMulti = kTileBytes /*Q*/ + 4 * kTileBytes /*K V x2*/ + kPBytes /*P*/ + 1024 + 4096;
+
+__global__ void __launch_bounds__(kThreadsMulti, 1)
+attn_fwd_tc_multi_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                         const __grid_constant__ CUtensorMap tm_v, const TcArgs p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sQ = smem; uint8_t* sK = sQ + kTileBytes; uint8_t* sV = sK + 2 * kTileBytes; uint8_t* sP = sV + 2 * kTileBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kPBytes);
+  uint64_t* bar_q = bars; uint64_t* kv_full = bars + 1; uint64_t* kv_empty = bars + 3;
+  uint64_t* s_ready = bars + 5; uint64_t* p_ready = bars + 6; uint64_t* o_ready = bars + 7;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  int* s_mask = reinterpret_cast<int*>(bars + 10);            // [2][128] per K/V stage
+  float* x_max = reinterpret_cast<float*>(s_mask + 256);       // [2][128] partial row max per column half
+  float* x_sum = x_max + 256;                                  // [2][128] partial row sum per column half
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int q0 = qt * kT;
+  const long long* toks = p.key_tokens + size_t(b) * p.Sk;
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tm_q); ptx::prefetch_tmap(&tm_k); ptx::prefetch_tmap(&tm_v);
+    ptx::mbar_init(bar_q, 1);
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
+    ptx::mbar_init(s_ready, 1); ptx::mbar_init(p_ready, 256); ptx::mbar_init(o_ready, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) { ptx::tmem_alloc(tmem_slot, 256); ptx::tmem_relinquish(); }
+  pdl_wait();
+  pdl_trigger();
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tO = tmem + 128;
+
+  int kv_end = p.Sk;
+  if (p.causal && toks[0] != 0) kv_end = min(p.Sk, q0 + kT);   // later key tiles are exactly zero-weight
+  const int ntiles = (kv_end + kT - 1) / kT;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const uint32_t aQ = ptx::smem_u32(sQ), aP = ptx::smem_u32(sP);
+      constexpr uint32_t idesc_kk = ptx::make_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t idesc_km = ptx::make_idesc_bf16(128, 64, 0, 1);
+      auto load_kv = [&](int j) {
+        const int st = j & 1;
+        ptx::mbar_expect_tx(&kv_full[st], 2 * kTileBytes);
+        ptx::tma_load_2d(sK + st * kTileBytes, &tm_k, &kv_full[st], h * kD, b * p.Sk + j * kT);
+        ptx::tma_load_2d(sV + st * kTileBytes, &tm_v, &kv_full[st], h * kD, b * p.Sk + j * kT);
+      };
+      ptx::mbar_expect_tx(bar_q, kTileBytes);
+      ptx::tma_load_2d(sQ, &tm_q, bar_q, h * kD, b * p.Sq + q0);
+      load_kv(0);
+      ptx::mbar_wait(bar_q, 0);
+      for (int j = 0; j < ntiles; ++j) {
+        const int st = j & 1;
+        const uint32_t aK = ptx::smem_u32(sK + st * kTileBytes), aV = ptx::smem_u32(sV + st * kTileBytes);
+        ptx::mbar_wait(&kv_full[st], (j >> 1) & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          ptx::umma_bf16(tS, ptx::make_smem_desc(aQ + k * 32, 16, 1024), ptx::make_smem_desc(aK + k * 32, 16, 1024), idesc_kk, k > 0);
+        ptx::umma_commit(s_ready);
+        if (j + 1 < ntiles) {
+          ptx::mbar_wait(&kv_empty[(j + 1) & 1], (((j + 1) >> 1) & 1) ^ 1);
+          load_kv(j + 1);
+        }
+        ptx::mbar_wait(p_ready, j & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          ptx::umma_bf16(tO, ptx::make_smem_desc(aP + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
+                         ptx::make_smem_desc(aV + k * 2048, kTileBytes, 1024), idesc_km, k > 0);
+        ptx::umma_commit(&kv_empty[st]);   // this K/V stage may be refilled once these MMAs retire
+        ptx::umma_commit(o_ready);
+      }
+    }
+  } else if (warp >= 2) {
+    const int quarter = warp & 3, half = (warp - 2) >> 2;
+    const int i = quarter * 32 + lane;
+    const uint32_t lane_base = uint32_t(quarter * 32) << 16;
+    const int e = threadIdx.x - 64;                              // 0..255
+    const bool row_ok = q0 + i < p.Sq;
+    float o[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) o[c] = 0.f;
+    float m = -INFINITY, l = 0.f;
+    for (int j = 0; j < ntiles; ++j) {
+      const int k0 = j * kT;
+      if (e < kT) s_mask[(j & 1) * kT + e] = (k0 + e >= p.Sk) ? 2 : (toks[k0 + e] == 0 ? 1 : 0);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      const int* mask = s_mask + (j & 1) * kT;
+      ptx::mbar_wait(s_ready, j & 1);
+      ptx::tc_fence_after();
+      float s[64];
+      float mx = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        tmem_ld32(tS + lane_base + (half * 2 + c) * 32, s + c * 32);
+#pragma unroll
+        for (int t = 0; t < 32; ++t) {
+          const int key = (half * 2 + c) * 32 + t;
+          const int mk = mask[key];
+          float v = s[c * 32 + t] * p.scale_log2;
+          if (mk == 1 || (p.causal && k0 + key > q0 + i)) v = kMasked;
+          if (mk == 2) v = -INFINITY;
+          s[c * 32 + t] = v;
+          mx = fmaxf(mx, v);
+        }
+      }
+      x_max[half * kT + i] = mx;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      const float m_new = fmaxf(m, fmaxf(x_max[i], x_max[kT + i]));   // finite: the first tile always holds a real key
+      const float corr = exp2f(m - m_new);
+      float sum = 0.f;
+#pragma unroll
+      for (int t = 0; t < 64; ++t) { s[t] = exp2f(s[t] - m_new); sum += s[t]; }
+      x_sum[half * kT + i] = sum;
+      store_row32(sP, i, half * 64, s);
+      store_row32(sP, i, half * 64 + 32, s + 32);
+      ptx::tc_fence_before();
+      ptx::fence_proxy_async();
+      ptx::mbar_arrive(p_ready);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      l = l * corr + (x_sum[i] + x_sum[kT + i]);
+      m = m_new;
+      ptx::mbar_wait(o_ready, j & 1);
+      ptx::tc_fence_after();
+      float ot[32];
+      tmem_ld32(tO + lane_base + half * 32, ot);
+#pragma unroll
+      for (int c = 0; c < 32; ++c) o[c] = o[c] * corr + ot[c];
+      ptx::tc_fence_before();
+    }
+    if (row_ok) {
+      const float inv = 1.0f / l;
+      bf16* dst = p.o + (size_t(b) * p.Sq + q0 + i) * p.ldo + h * kD + half * 32;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 u;
+        u.x = ptx::pack_bf16x2(o[q * 8] * inv, o[q * 8 + 1] * inv); u.y = ptx::pack_bf16x2(o[q * 8 + 2] * inv, o[q * 8 + 3] * inv);
+        u.z = ptx::pack_bf16x2(o[q * 8 + 4] * inv, o[q * 8 + 5] * inv); u.w = ptx::pack_bf16x2(o[q * 8 + 6] * inv, o[q * 8 + 7] * inv);
+        *reinterpret_cast<uint4*>(dst + q * 8) = u;
+      }
+      if (half == 0 && p.lse) reinterpret_cast<float2*>(p.lse)[(size_t(b) * p.H + h) * p.Sq + q0 + i] = make_float2(m, log2f(l));
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { ptx::tc_fence_after(); ptx::tmem_dealloc(tmem, 256); }
+}
+
 // ---------------------------------------------------------------------------------------------------------- backward, any length
 // One CTA per (128-key tile, head, batch) walks the 128-query tiles that can see those keys.  Per (q tile, kv tile) pair:
 //   S = Q K^T, dP = dO V^T -> threads: P = exp2(s - m_i - log2 l_i), dS = P (dP - delta_i) -> smem ->
@@ -347,8 +507,6 @@ struct TcMultiArgs {
   int H, Sq, Sk, causal;
   float scale, scale_log2;
 };
-
-constexpr int kThreadsMulti = 320;  // warp 0: TMA + MMA issue, warp 1: TMEM allocation, warps 2-9: two threads per row (64 keys each)
 
 __global__ void __launch_bounds__(kThreadsMulti, 1)
 attn_bwd_tc_multi_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
@@ -578,6 +736,33 @@ attn_bwd_dq_out_kernel(const float* __restrict__ dq_acc, bf16* __restrict__ dq, 
 }
 
 }  // namespace
+
+// Measured on B200 (scripts/kernel_bench.py long / big): this forward is on par with the mma.sync kernel (63 vs 67 us causal,
+// 91 vs 89 us non-causal at B8 H8 S1024; 30 vs 26 us at S256) because one CTA serialises S -> softmax -> PV, so it is opt-in
+// (B200XF_ATTENTION_TC_FWD_MULTI=1, read at every call) until it ping-pongs two query tiles per CTA.
+bool attention_tc_fwd_multi_supported(const AttnArgs& a) {
+  const char* e = getenv("B200XF_ATTENTION_TC_FWD_MULTI");
+  return e && atoi(e) != 0 && a.dk == kD && a.Sq > 0 && a.Sk > 0;
+}
+
+int attention_fwd_tc_multi(const AttnArgs& a, cudaStream_t stream) {
+  CUtensorMap tq, tk, tv;
+  const uint64_t cols = uint64_t(a.H) * kD;
+  B200XF_TRY(tensor_map_2d(a.q, cols, uint64_t(a.B) * a.Sq, a.ldq, kT, &tq, 0));
+  B200XF_TRY(tensor_map_2d(a.k, cols, uint64_t(a.B) * a.Sk, a.ldk, kT, &tk, 0));
+  B200XF_TRY(tensor_map_2d(a.v, cols, uint64_t(a.B) * a.Sk, a.ldv, kT, &tv, 0));
+  TcArgs p{};
+  p.key_tokens = a.key_tokens; p.o = a.o; p.ldo = a.ldo; p.lse = a.lse;
+  p.H = a.H; p.Sq = a.Sq; p.Sk = a.Sk; p.causal = a.causal;
+  p.scale = 1.0f / sqrtf(float(a.dk)); p.scale_log2 = p.scale * kLog2e;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] { attr_err = cudaFuncSetAttribute(attn_fwd_tc_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemFwdMulti); });
+  if (attr_err != cudaSuccess) return set_error("cudaFuncSetAttribute(attn_fwd_tc_multi): %s", cudaGetErrorString(attr_err));
+  B200XF_CUDA(launch_k(attn_fwd_tc_multi_kernel, dim3((a.Sq + kT - 1) / kT, a.H, a.B), kThreadsMulti, kSmemFwdMulti, stream, tq, tk, tv, p));
+  count_launch();
+  return 0;
+}
 
 bool attention_tc_multi_supported(const AttnArgs& a) {
   static int enabled = -1;

@@ -96,6 +96,8 @@ int attention_fwd_tc(const AttnArgs& a, cudaStream_t stream);
 int attention_bwd_tc(const AttnArgs& a, cudaStream_t stream);
 // tcgen05 multi-tile backward (any Sq, Sk; head size 64; needs AttnArgs::dq_acc)
 bool attention_tc_multi_supported(const AttnArgs& a);
+bool attention_tc_fwd_multi_supported(const AttnArgs& a);
+int attention_fwd_tc_multi(const AttnArgs& a, cudaStream_t stream);
 int attention_bwd_tc_multi(const AttnArgs& a, cudaStream_t stream);
 
 // ---- LayerNorm (+ optional residual add) fwd / bwd (transformer_model.py:187-188,198,204)
