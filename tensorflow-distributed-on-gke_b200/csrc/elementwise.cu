@@ -643,6 +643,7 @@ int ce_finalize(const float* row_loss, const int* row_correct, const int* nonpad
 namespace {
 // TF-form Adam (ResourceApplyAdam) with the reference's warm-up schedule evaluated on the device from
 // `iterations` (the value BEFORE this step's increment, so the very first step has lr == 0).
+constexpr int kAdamPerBlock = 8;
 __global__ void __launch_bounds__(256)
 adam_kernel(float4* __restrict__ w, float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v,
             uint2* __restrict__ wb, size_t n4, const long long* __restrict__ iterations, AdamHyper h, int zero_grad) {
@@ -653,7 +654,13 @@ adam_kernel(float4* __restrict__ w, float4* __restrict__ g, float4* __restrict__
   const float t = step + 1.0f;
   const float alpha = lr * sqrtf(1.0f - powf(h.beta2, t)) / (1.0f - powf(h.beta1, t));
   const float c1 = 1.0f - h.beta1, c2 = 1.0f - h.beta2;
-  for (size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x; i < n4; i += size_t(gridDim.x) * blockDim.x) {
+  // short-lived CTAs (8 x 256 float4 each): the update runs on a low-priority stream under the backward pass, and the
+  // block scheduler can only hand an SM back to the critical path when a CTA retires
+  const size_t base = size_t(blockIdx.x) * (kAdamPerBlock * 256) + threadIdx.x;
+#pragma unroll 2
+  for (int kk = 0; kk < kAdamPerBlock; ++kk) {
+    const size_t i = base + size_t(kk) * 256;
+    if (i >= n4) break;
     float4 W = w[i], M = m[i], V = v[i];
     const float4 G = g[i];
     // each operation rounded separately, exactly as the expression is written (no FMA contraction)
@@ -678,7 +685,7 @@ int adam_step(float* w, float* g, float* m, float* v, bf16* w_bf16, size_t n, co
   if (n % 4) return set_error("adam: n=%zu must be a multiple of 4", n);
   if (n == 0) return 0;
   const size_t n4 = n / 4;
-  const int grid = int(std::min<size_t>((n4 + 255) / 256, size_t(num_sms()) * 8));
+  const int grid = int((n4 + size_t(kAdamPerBlock) * 256 - 1) / (size_t(kAdamPerBlock) * 256));
   B200XF_CUDA(launch_k(adam_kernel, grid, 256, 0, stream, reinterpret_cast<float4*>(w), reinterpret_cast<float4*>(g), reinterpret_cast<float4*>(m),
                        reinterpret_cast<float4*>(v), reinterpret_cast<uint2*>(w_bf16), n4, iterations_dev, h, zero_grad));
   B200XF_CUDA(cudaGetLastError());
