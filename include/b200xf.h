@@ -121,7 +121,11 @@ int b200xf_dropout_mask(b200xf_ctx* ctx, int site, int rows, int cols, float* ou
 int b200xf_comm_unique_id(void* unique_id_128_bytes);
 int b200xf_comm_init(b200xf_ctx* ctx, const void* unique_id_128_bytes, int rank, int world);
 int b200xf_comm_destroy(b200xf_ctx* ctx);
-/* All-reduce (SUM, fp32, in place) of `count` floats at DEVICE pointer on the context's comm stream. */
+/* With more than one rank a train step reduce-scatters each gradient bucket, applies Adam to the local 1/world shard and
+ * all-gathers the updated weights (same wire bytes as an all-reduce, 1/world of the optimizer traffic): every rank ends
+ * with identical fp32 weights, but adam_m / adam_v are then only maintained for the local shard of each bucket.
+ * B200XF_SHARDED_UPDATE=0 selects all-reduce + replicated Adam.
+ * All-reduce (SUM, fp32, in place) of `count` floats at DEVICE pointer on the context's comm stream. */
 int b200xf_allreduce_bucket(b200xf_ctx* ctx, float* device_ptr, int64_t count);
 
 /* ---- per-kernel entry points (unit tests, ncu).  All pointers are DEVICE pointers, `stream` a cudaStream_t. */

@@ -30,6 +30,8 @@ struct NcclApi {
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*ReduceScatter)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*GroupStart)() = nullptr;
   ncclResult_t (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
@@ -51,7 +53,7 @@ static NcclApi* nccl_api() {
 #define LOAD(field, sym) api.field = reinterpret_cast<decltype(api.field)>(dlsym(api.handle, sym))
   LOAD(GetUniqueId, "ncclGetUniqueId"); LOAD(CommInitRank, "ncclCommInitRank"); LOAD(CommDestroy, "ncclCommDestroy");
   LOAD(AllReduce, "ncclAllReduce"); LOAD(GroupStart, "ncclGroupStart"); LOAD(GroupEnd, "ncclGroupEnd");
-  LOAD(GetErrorString, "ncclGetErrorString");
+  LOAD(GetErrorString, "ncclGetErrorString"); LOAD(ReduceScatter, "ncclReduceScatter"); LOAD(AllGather, "ncclAllGather");
 #undef LOAD
   if (!api.GetUniqueId || !api.CommInitRank || !api.AllReduce || !api.CommDestroy) { api.handle = nullptr; return nullptr; }
   return &api;
@@ -96,7 +98,9 @@ void Context::build_layout() {
   vt_ld = int(align_up(size_t(Vt), 8));
   size_t cur = 0;
   sections.clear();
-  auto close_section = [&](size_t begin) { sections.push_back({begin, cur}); };
+  // every section ends on a 4096-element boundary, so any bucket of sections splits into equal 64-element-aligned
+  // shards for up to 64 ranks (reduce-scatter / all-gather of the sharded update)
+  auto close_section = [&](size_t begin) { cur = align_up(cur, 4096); sections.push_back({begin, cur}); };
 
   size_t begin = cur;
   final_layer = add_dense(cur, d, Vt, vt_ld);
@@ -342,6 +346,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   if (const char* e = getenv("B200XF_SIDE_WGRAD")) side_on = atoi(e) != 0;
   if (const char* e = getenv("B200XF_PHASE_TIMING")) phase_timing = atoi(e) != 0;
   if (const char* e = getenv("B200XF_GRAPH")) use_graph = atoi(e) != 0;
+  if (const char* e = getenv("B200XF_SHARDED_UPDATE")) sharded_update = atoi(e) != 0;
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_ready, cudaEventDisableTiming));
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_done, cudaEventDisableTiming));
   return 0;
@@ -766,9 +771,23 @@ int Context::section_done() {
   B200XF_TRY(flush_reductions());
   B200XF_CUDA(cudaEventRecord(ev_ready, stream));
   B200XF_CUDA(cudaStreamWaitEvent(comm_stream, ev_ready, 0));
-  if (comm) B200XF_TRY(allreduce(grads + bucket_begin, end - bucket_begin, comm_stream));
-  B200XF_TRY(adam_step(params + bucket_begin, grads + bucket_begin, adam_m + bucket_begin, adam_v + bucket_begin,
-                       shadow + bucket_begin, end - bucket_begin, iterations_dev, adam, 1, comm_stream));
+  const size_t n = end - bucket_begin;
+  NcclApi* api = comm ? nccl_api() : nullptr;
+  if (comm && sharded_update && world > 1 && api->ReduceScatter && api->AllGather && n % (size_t(world) * 64) == 0) {
+    // all-reduce = reduce-scatter + all-gather: put the Adam update between the two halves, on this rank's 1/world
+    // shard only (same bytes on the wire, 1/world of the optimizer's HBM traffic), then gather the updated fp32
+    // weights and refresh the bf16 operand copy / clear the gradients of the whole bucket in one pass
+    const size_t sh = n / world, off = bucket_begin + size_t(rank) * sh;
+    ncclComm_t c = static_cast<ncclComm_t>(comm);
+    B200XF_NCCL(api->ReduceScatter(grads + bucket_begin, grads + off, sh, ncclFloat32, ncclSum, c, comm_stream));
+    B200XF_TRY(adam_step(params + off, grads + off, adam_m + off, adam_v + off, nullptr, sh, iterations_dev, adam, 0, comm_stream));
+    B200XF_NCCL(api->AllGather(params + off, params + bucket_begin, sh, ncclFloat32, c, comm_stream));
+    B200XF_TRY(refresh_shadow_zero_grad(params + bucket_begin, shadow + bucket_begin, grads + bucket_begin, n, comm_stream));
+  } else {
+    if (comm) B200XF_TRY(allreduce(grads + bucket_begin, n, comm_stream));
+    B200XF_TRY(adam_step(params + bucket_begin, grads + bucket_begin, adam_m + bucket_begin, adam_v + bucket_begin,
+                         shadow + bucket_begin, n, iterations_dev, adam, 1, comm_stream));
+  }
   bucket_begin = end;
   return 0;
 }

@@ -84,6 +84,9 @@ struct Context {
   cudaStream_t comm_stream = nullptr;
   cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
   size_t bucket_bytes = size_t(32) << 20, bucket_begin = 0, next_section = 0;
+  // With several ranks each bucket is reduce-scattered, updated on the local 1/world shard and all-gathered (Adam m / v
+  // are then only maintained for the local shard of every bucket).  B200XF_SHARDED_UPDATE=0 keeps the replicated update.
+  bool sharded_update = true;
   bool overlap_update = false;
   bool overlap_single = true;   // single GPU too: each bucket's Adam runs on the update stream under the rest of backward (B200XF_OVERLAP_UPDATE=0 disables)
 

@@ -693,6 +693,35 @@ int adam_step(float* w, float* g, float* m, float* v, bf16* w_bf16, size_t n, co
   return 0;
 }
 
+namespace {
+__global__ void __launch_bounds__(256)
+refresh_kernel(const float4* __restrict__ w, uint2* __restrict__ wb, float4* __restrict__ g, size_t n4) {
+  pdl_wait();
+  pdl_trigger();
+  const size_t base = size_t(blockIdx.x) * (kAdamPerBlock * 256) + threadIdx.x;
+#pragma unroll 4
+  for (int kk = 0; kk < kAdamPerBlock; ++kk) {
+    const size_t i = base + size_t(kk) * 256;
+    if (i >= n4) break;
+    const float4 W = w[i];
+    uint2 u; u.x = ptx::pack_bf16x2(W.x, W.y); u.y = ptx::pack_bf16x2(W.z, W.w);
+    wb[i] = u;
+    g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+}  // namespace
+
+int refresh_shadow_zero_grad(const float* w, bf16* shadow, float* g, size_t n, cudaStream_t stream) {
+  if (n % 4) return set_error("refresh: n must be a multiple of 4");
+  if (n == 0) return 0;
+  const size_t n4 = n / 4;
+  const int grid = int((n4 + size_t(kAdamPerBlock) * 256 - 1) / (size_t(kAdamPerBlock) * 256));
+  B200XF_CUDA(launch_k(refresh_kernel, grid, 256, 0, stream, reinterpret_cast<const float4*>(w), reinterpret_cast<uint2*>(shadow),
+                       reinterpret_cast<float4*>(g), n4));
+  count_launch();
+  return 0;
+}
+
 int increment_counter(long long* iterations_dev, cudaStream_t stream) {
   B200XF_CUDA(launch_k(increment_kernel, 1, 1, 0, stream, iterations_dev));
   B200XF_CUDA(cudaGetLastError());

@@ -142,6 +142,8 @@ struct AdamHyper { float beta1, beta2, eps, rsqrt_d_model, warmup_pow_m15; };  /
 int adam_step(float* w, float* g, float* m, float* v, bf16* w_bf16, size_t n, const long long* iterations_dev,
               AdamHyper h, int zero_grad, cudaStream_t stream);
 int increment_counter(long long* iterations_dev, cudaStream_t stream);
+// shadow = bf16(w), g = 0 over n elements (after the all-gather of a sharded update)
+int refresh_shadow_zero_grad(const float* w, bf16* shadow, float* g, size_t n, cudaStream_t stream);
 
 // ---- small helpers
 // partials [colsum_parts(rows, cols)][cols] of the column sums of a bf16 matrix
