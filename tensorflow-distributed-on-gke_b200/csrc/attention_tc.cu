@@ -38,7 +38,8 @@ struct TcArgs {
 };
 
 // smem: sQ sK sV sdO (16 KB each) | sP (32 KB) | sdS (32 KB) | barriers
-constexpr int kSmemBwd = 4 * kTileBytes + 2 * kPBytes + 1024 /*alignment slack*/ + 1024 /*barriers, TMEM slot, key mask*/;
+constexpr int kSmemBwd = 4 * kTileBytes + 2 * kPBytes + 1024 /*alignment slack*/ + 4096 /*barriers, TMEM slot, key mask, row exchange*/;
+constexpr int kThreads2 = 320;   // warp 0: TMA + MMA issue, warp 1: TMEM allocation, warps 2-9: two threads per row
 
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* f) {
   uint32_t v[32];
@@ -61,7 +62,7 @@ __device__ __forceinline__ void store_row32(uint8_t* base, int row, int c0, cons
   }
 }
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads2, 1)
 attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                    const __grid_constant__ CUtensorMap tm_v, const __grid_constant__ CUtensorMap tm_do, const TcArgs p) {
   extern __shared__ uint8_t smem_raw[];
@@ -73,18 +74,19 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
   uint64_t* bars = reinterpret_cast<uint64_t*>(sdS + kPBytes);  // 0 load, 1 S/dP ready, 2 P/dS written, 3 outputs ready
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
   int* s_mask = reinterpret_cast<int*>(bars + 6);               // [128] key mask: 0 keep, 1 PAD, 2 past Sk
+  float* xch = reinterpret_cast<float*>(s_mask + kT);           // [3][2][128] partial max / sum / delta of the two column halves
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int h = blockIdx.x, b = blockIdx.y;
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tm_q); ptx::prefetch_tmap(&tm_k); ptx::prefetch_tmap(&tm_v); ptx::prefetch_tmap(&tm_do);
-    ptx::mbar_init(&bars[0], 1); ptx::mbar_init(&bars[1], 1); ptx::mbar_init(&bars[2], 128); ptx::mbar_init(&bars[3], 1);
+    ptx::mbar_init(&bars[0], 1); ptx::mbar_init(&bars[1], 1); ptx::mbar_init(&bars[2], 256); ptx::mbar_init(&bars[3], 1);
     ptx::fence_barrier_init();
   }
   if (warp == 1) { ptx::tmem_alloc(tmem_slot, 512); ptx::tmem_relinquish(); }
   pdl_wait();   // everything above overlaps the tail of the previous kernel
   pdl_trigger();
-  if (warp >= 2) {
+  if (warp >= 2 && warp < 6) {
     const int j = threadIdx.x - 64;
     s_mask[j] = (j >= p.Sk) ? 2 : (p.key_tokens[size_t(b) * p.Sk + j] == 0 ? 1 : 0);
   }
@@ -132,53 +134,55 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
       ptx::umma_commit(&bars[3]);
     }
   } else if (warp >= 2) {
+    // two threads per row: warps 2-5 take keys 0..63 (output columns 0..31), warps 6-9 keys 64..127 (columns 32..63);
+    // the row max, sum and delta are combined through shared memory
     const int quarter = warp & 3;                 // TMEM lane quarter of this warp
+    const int half = (warp - 2) >> 2;
     const int i = quarter * 32 + lane;            // query row (and, in the epilogue, key row) of this thread
     const uint32_t lane_base = uint32_t(quarter * 32) << 16;
     ptx::mbar_wait(&bars[1], 0);
     ptx::tc_fence_after();
     const bool row_ok = i < p.Sq;
-    // pass 1: masked, scaled scores (log2 domain) -> row max and sum
-    float s[kT];
+    float s[64], dp[64];
     float mx = -INFINITY;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      tmem_ld32(tS + lane_base + c * 32, s + c * 32);
+    for (int c = 0; c < 2; ++c) {
+      tmem_ld32(tS + lane_base + (half * 2 + c) * 32, s + c * 32);
+      tmem_ld32(tdP + lane_base + (half * 2 + c) * 32, dp + c * 32);
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
-        const int key = c * 32 + j;
+        const int key = (half * 2 + c) * 32 + j;
         const int mk = s_mask[key];
-        float v = s[key] * p.scale_log2;
+        float v = s[c * 32 + j] * p.scale_log2;
         if (mk == 1 || (p.causal && key > i)) v = kMasked;
         if (mk == 2) v = -INFINITY;
-        s[key] = v;
+        s[c * 32 + j] = v;
         mx = fmaxf(mx, v);
       }
     }
+    xch[half * kT + i] = mx;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    mx = fmaxf(xch[i], xch[kT + i]);              // finite: key 0 always exists
     float sum = 0.f;
 #pragma unroll
-    for (int j = 0; j < kT; ++j) { s[j] = exp2f(s[j] - mx); sum += s[j]; }
+    for (int j = 0; j < 64; ++j) { s[j] = exp2f(s[j] - mx); sum += s[j]; }
+    xch[2 * kT + half * kT + i] = sum;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    sum = xch[2 * kT + i] + xch[3 * kT + i];
     const float inv = row_ok ? 1.0f / sum : 0.f;  // rows past Sq contribute nothing to dK / dV
+    float delta = 0.f;                            // delta = sum_j P dP (exact, fp32)
 #pragma unroll
-    for (int j = 0; j < kT; ++j) s[j] *= inv;
-    // pass 2: delta = sum_j P dP (exact, fp32)
-    float delta = 0.f;
+    for (int j = 0; j < 64; ++j) { s[j] *= inv; delta += s[j] * dp[j]; }
+    xch[4 * kT + half * kT + i] = delta;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    delta = xch[4 * kT + i] + xch[5 * kT + i];
+    // P and dS = P (dP - delta) -> shared memory (bf16, swizzled operand layout)
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      float dp[32];
-      tmem_ld32(tdP + lane_base + c * 32, dp);
+    for (int c = 0; c < 2; ++c) {
+      store_row32(sP, i, half * 64 + c * 32, s + c * 32);
 #pragma unroll
-      for (int j = 0; j < 32; ++j) delta += s[c * 32 + j] * dp[j];
-    }
-    // pass 3: write P and dS = P (dP - delta) to shared memory (bf16, swizzled operand layout)
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      float dp[32];
-      tmem_ld32(tdP + lane_base + c * 32, dp);
-      store_row32(sP, i, c * 32, s + c * 32);
-#pragma unroll
-      for (int j = 0; j < 32; ++j) dp[j] = s[c * 32 + j] * (dp[j] - delta);
-      store_row32(sdS, i, c * 32, dp);
+      for (int j = 0; j < 32; ++j) dp[c * 32 + j] = s[c * 32 + j] * (dp[c * 32 + j] - delta);
+      store_row32(sdS, i, half * 64 + c * 32, dp + c * 32);
     }
     ptx::tc_fence_before();
     ptx::fence_proxy_async();
@@ -186,21 +190,18 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
 
     ptx::mbar_wait(&bars[3], 0);
     ptx::tc_fence_after();
-    // epilogue: thread i owns query row i of dQ and key row i of dK, dV (64 fp32 each in TMEM)
+    // epilogue: row i of dQ (query i) and of dK, dV (key i); this thread converts 32 of the 64 columns
     // (the TMEM loads are warp-collective: every thread executes them, only rows inside the sequence store)
     auto store_row = [&](uint32_t taddr, bf16* dst, float mul, bool ok) {
+      float f[32];
+      tmem_ld32(taddr + lane_base + half * 32, f);
+      if (ok) {
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        float f[32];
-        tmem_ld32(taddr + lane_base + c * 32, f);
-        if (ok) {
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            uint4 u;
-            u.x = ptx::pack_bf16x2(f[q * 8] * mul, f[q * 8 + 1] * mul); u.y = ptx::pack_bf16x2(f[q * 8 + 2] * mul, f[q * 8 + 3] * mul);
-            u.z = ptx::pack_bf16x2(f[q * 8 + 4] * mul, f[q * 8 + 5] * mul); u.w = ptx::pack_bf16x2(f[q * 8 + 6] * mul, f[q * 8 + 7] * mul);
-            *reinterpret_cast<uint4*>(dst + c * 32 + q * 8) = u;
-          }
+        for (int q = 0; q < 4; ++q) {
+          uint4 u;
+          u.x = ptx::pack_bf16x2(f[q * 8] * mul, f[q * 8 + 1] * mul); u.y = ptx::pack_bf16x2(f[q * 8 + 2] * mul, f[q * 8 + 3] * mul);
+          u.z = ptx::pack_bf16x2(f[q * 8 + 4] * mul, f[q * 8 + 5] * mul); u.w = ptx::pack_bf16x2(f[q * 8 + 6] * mul, f[q * 8 + 7] * mul);
+          *reinterpret_cast<uint4*>(dst + half * 32 + q * 8) = u;
         }
       }
     };
@@ -839,7 +840,7 @@ int attention_bwd_tc(const AttnArgs& a, cudaStream_t stream) {
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] { attr_err = cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBwd); });
   if (attr_err != cudaSuccess) return set_error("cudaFuncSetAttribute(attn_bwd_tc): %s", cudaGetErrorString(attr_err));
-  B200XF_CUDA(launch_k(attn_bwd_tc_kernel, dim3(a.H, a.B), kThreads, kSmemBwd, stream, tq, tk, tv, tdo, p));
+  B200XF_CUDA(launch_k(attn_bwd_tc_kernel, dim3(a.H, a.B), kThreads2, kSmemBwd, stream, tq, tk, tv, tdo, p));
   count_launch();
   return 0;
 }
