@@ -25,8 +25,10 @@ def synthetic_batch(B, S, T_plus_1, vin, vtgt, seed, ragged=False):
         out = np.zeros((n, L), dtype=np.int64)
         for b in range(n):
             ln = int(rng.integers((L + 1) // 2, L + 1)) if ragged else L
-            ln = max(ln, 2)
+            ln = min(max(ln, 2), L)
             out[b, 0] = 2
+            if L == 1:
+                continue
             out[b, 1:ln - 1] = rng.integers(4, V, size=max(ln - 2, 0))
             out[b, ln - 1] = 3
         return out
