@@ -348,7 +348,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       if (lane == 0) ptx::mbar_arrive(&tmem_empty[as]);
       if (it == 0 && warp == 2 && lane == 0) stamp(p, 5);
     }
-    if (p.d_tma && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // staging smem must outlive the stores
+    // the staging buffers must outlive the stores' reads of them; the writes themselves complete with the grid
+    if (p.d_tma && lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
   }
 
   ptx::tc_fence_before();

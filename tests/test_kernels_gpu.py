@@ -225,7 +225,7 @@ def test_positional_encoding_matches_reference_kat():
 
 
 # ------------------------------------------------------------------------------------------ cross-entropy
-@pytest.mark.parametrize("rows,V,workers", [(2560, 7010, 1), (512, 32000, 3), (64, 50, 1)])
+@pytest.mark.parametrize("rows,V,workers", [(2560, 7010, 1), (512, 32000, 3), (64, 50, 1), (128, 12345, 1), (64, 40001, 2)])
 def test_vocab_ce(rows, V, workers):
     g = torch.Generator(device=DEV).manual_seed(13)
     ld = (V + 7) // 8 * 8
