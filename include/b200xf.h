@@ -143,6 +143,10 @@ int b200xf_gemm_bf16(const void* a, int lda, int a_mn, const void* b, int ldb, i
  * records %globaltimer stamps per CTA (start, set-up done, first operands landed, last MMA issued, accumulator ready,
  * epilogue done, exit).  Pass NULL to switch it off. */
 int b200xf_debug_gemm_trace(void* device_u64_buffer);
+/* Same, for a whole step: the buffer holds `slots` x 148 x 8 u64 and successive launches use successive slots (wrapping).
+ * Stamp 7 of a slot's first CTA is (M << 44 | N << 24 | K << 4 | a_mn << 1 | b_mn).  Launches captured into a CUDA graph
+ * keep their slot, so replaying the step refills the ring.  No counterpart in the reference (debugging aid). */
+int b200xf_debug_gemm_trace_ring(void* device_u64_buffer, int slots);
 
 /* scaled_dot_product_attention + masks + split/merge heads (transformer_model.py:56-70,73-109,124-131,160-163).
  * q [B*Sq, ldq], k/v [B*Sk, ld*], o [B*Sq, ldo] bf16, head h in columns [h*dk,(h+1)*dk); key_tokens [B,Sk] int64;

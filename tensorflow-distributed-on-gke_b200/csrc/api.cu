@@ -153,6 +153,12 @@ int b200xf_debug_gemm_trace(void* device_u64_buffer) {
   return 0;
 }
 
+int b200xf_debug_gemm_trace_ring(void* device_u64_buffer, int slots) {
+  if (device_u64_buffer && slots <= 0) return set_error("gemm trace ring: slots must be positive");
+  gemm_set_trace(static_cast<unsigned long long*>(device_u64_buffer), slots);
+  return 0;
+}
+
 int b200xf_attention_fwd(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, void* o, int ldo, float* lse,
                          const int64_t* key_tokens, int causal, int B, int H, int Sq, int Sk, int dk, void* stream) {
   AttnArgs a;

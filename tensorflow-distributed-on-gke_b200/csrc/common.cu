@@ -40,6 +40,16 @@ bool pdl_enabled() {
   return v != 0;
 }
 
+int stream_priority(cudaStream_t stream) {
+  // streams are few and long-lived; a stale entry (handle reused after destroy) only mis-states a scheduling hint
+  thread_local cudaStream_t keys[8]; thread_local int vals[8]; thread_local int used = 0;
+  for (int i = 0; i < used; ++i) if (keys[i] == stream) return vals[i];
+  int prio = 0;
+  if (cudaStreamGetPriority(stream, &prio) != cudaSuccess) { (void)cudaGetLastError(); prio = 0; }
+  if (used < 8) { keys[used] = stream; vals[used] = prio; ++used; }
+  return prio;
+}
+
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 long long launches_total() { return g_launches.load(std::memory_order_relaxed); }
 

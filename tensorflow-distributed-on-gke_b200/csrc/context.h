@@ -87,6 +87,11 @@ struct Context {
   // With several ranks each bucket is reduce-scattered, updated on the local 1/world shard and all-gathered (Adam m / v
   // are then only maintained for the local shard of every bucket).  B200XF_SHARDED_UPDATE=0 keeps the replicated update.
   bool sharded_update = true;
+  // the bf16 weight copy is only written by the optimizer, never by the kernel just before a forward / data-gradient
+  // GEMM on the compute stream, so those GEMMs may fetch their first weight tiles ahead of the dependency wait
+  int weights_static = 1;  // B200XF_WEIGHT_PREFETCH=0 disables
+  bool bucket_bytes_set = false;  // B200XF_BUCKET_MB given
+  bool bucket_join = true;  // a closing bucket makes the compute stream wait for the side stream (B200XF_BUCKET_JOIN)
   bool overlap_update = false;
   bool overlap_single = true;   // single GPU too: each bucket's Adam runs on the update stream under the rest of backward (B200XF_OVERLAP_UPDATE=0 disables)
 
@@ -112,7 +117,7 @@ struct Context {
   int ln_bwd(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const LnP& p, size_t dcol_off, int rows, int drop_site);
   int colsum(const bf16* x, int ld, int rows, int cols, size_t dst_off);
   float* red_alloc(size_t floats);
-  int flush_reductions();
+  int flush_reductions(cudaStream_t on = nullptr);  // the partials scratch is not reused within a step, so this may run late
   int last_B = 0, last_S = 0, last_T = 0; const long long *last_inp = nullptr, *last_tgt = nullptr;
   int attention_weights(int layer, int block, float* out);
   int check_shapes(int B, int S, int T);

@@ -787,7 +787,11 @@ __global__ void cast_back_kernel(const bf16* __restrict__ in, int ldi, float* __
 
 int colsum_parts(int rows, int cols) {
   const int colblocks = (cols + 63) / 64;
-  const int want = (2 * num_sms() + colblocks - 1) / colblocks;
+  // enough CTAs to fill the machine, and never more than 256 rows per CTA: these sums run on the side stream next to
+  // GEMM CTAs that need a whole SM's shared memory, which the block scheduler can only hand over when every small CTA
+  // on that SM has retired -- long-lived CTAs here (one strip of 4096 rows under the vocabulary projection) stalled
+  // the critical path for their whole duration
+  const int want = std::max((2 * num_sms() + colblocks - 1) / colblocks, (rows + 255) / 256);
   return std::max(1, std::min(want, (rows + 127) / 128));
 }
 

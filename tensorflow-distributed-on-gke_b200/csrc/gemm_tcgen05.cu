@@ -52,6 +52,7 @@ struct GemmParams {
   float alpha;
   unsigned long long* trace;  // debug: 8 globaltimer stamps per CTA (null in production)
   DropArgs drop;
+  int b_static;  // B is not written by the kernel launched just before this one: its first tiles may be fetched before griddepcontrol.wait
 };
 
 // bias add, ReLU, residual add / ReLU mask on 32 accumulator columns [col0, col0+32) of one output row.
@@ -124,7 +125,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  if (threadIdx.x == 0) stamp(p, 0);
+  if (threadIdx.x == 0) {
+    stamp(p, 0);
+    if (p.trace && blockIdx.x == 0)  // slot 7 of CTA 0 identifies the launch: M, N, K and the operand majors
+      p.trace[7] = (static_cast<unsigned long long>(p.M) << 44) | (static_cast<unsigned long long>(p.N) << 24) |
+                   (static_cast<unsigned long long>(p.K) << 4) | (A_MN << 1) | B_MN;
+  }
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmap_a);
@@ -142,12 +148,31 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
+  const int total_kb = (p.K + BK - 1) / BK;
+  // Weights (the B operand of the forward and data-gradient GEMMs) do not depend on the previous kernel: start
+  // fetching the first tile's B blocks while that kernel is still finishing, and only the A blocks after the wait.
+  int prefetched = 0;
+  if (p.b_static && threadIdx.x == 0 && int(blockIdx.x) < total_tiles) {
+    const int t = blockIdx.x;
+    const int tn = (t / p.tiles_m) % p.tiles_n, z = t / (p.tiles_m * p.tiles_n);
+    const int kb0 = z * p.kb_per_split;
+    const int kb1 = min(total_kb, kb0 + p.kb_per_split);
+    prefetched = min(C::kStages, kb1 - kb0);
+    for (int s = 0; s < prefetched; ++s) {
+      uint8_t* sb = smem + s * C::kStageBytes + C::kABytes;
+      ptx::mbar_expect_tx(&full_bar[s], C::kStageBytes);
+      if (B_MN) {
+#pragma unroll
+        for (int c = 0; c < BN / 64; ++c) ptx::tma_load_2d(sb + c * 8192, &tmap_b, &full_bar[s], tn * BN + c * 64, (kb0 + s) * BK);
+      } else {
+        ptx::tma_load_2d(sb, &tmap_b, &full_bar[s], (kb0 + s) * BK, tn * BN);
+      }
+    }
+  }
   pdl_wait();     // barrier init, TMEM allocation and descriptor prefetch above overlap the previous kernel's tail
   pdl_trigger();
   if (threadIdx.x == 0) stamp(p, 1);
-
-  const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
-  const int total_kb = (p.K + BK - 1) / BK;
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (one lane)
@@ -158,17 +183,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         const int kb0 = z * p.kb_per_split;
         const int kb1 = min(total_kb, kb0 + p.kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
-          ptx::mbar_wait(&empty_bar[s], ph ^ 1);
+          const bool have_b = prefetched > 0;  // this stage was armed and its B block requested before the wait
+          if (have_b) --prefetched;
+          if (!have_b) ptx::mbar_wait(&empty_bar[s], ph ^ 1);
           uint8_t* sa = smem + s * C::kStageBytes;
           uint8_t* sb = sa + C::kABytes;
-          ptx::mbar_expect_tx(&full_bar[s], C::kStageBytes);
+          if (!have_b) ptx::mbar_expect_tx(&full_bar[s], C::kStageBytes);
           if (A_MN) {
 #pragma unroll
             for (int c = 0; c < BM / 64; ++c) ptx::tma_load_2d(sa + c * 8192, &tmap_a, &full_bar[s], tm * BM + c * 64, kb * BK);
           } else {
             ptx::tma_load_2d(sa, &tmap_a, &full_bar[s], kb * BK, tm * BM);
           }
-          if (B_MN) {
+          if (have_b) {
+            // nothing: B is on its way
+          } else if (B_MN) {
 #pragma unroll
             for (int c = 0; c < BN / 64; ++c) ptx::tma_load_2d(sb + c * 8192, &tmap_b, &full_bar[s], tn * BN + c * 64, kb * BK);
           } else {
@@ -385,6 +414,8 @@ struct MapKey {
   }
 };
 unsigned long long* g_gemm_trace = nullptr;
+int g_gemm_trace_slots = 1;   // ring of per-launch trace slots (148 CTAs x 8 stamps each)
+int g_gemm_trace_next = 0;
 std::map<MapKey, CUtensorMap> g_map_cache;
 std::mutex g_map_mutex;
 
@@ -440,7 +471,7 @@ int launch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& t
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   if (a.M <= 0 || a.N <= 0 || a.K <= 0) return set_error("gemm: empty problem M=%d N=%d K=%d", a.M, a.N, a.K);
   if (a.accumulate && !a.d_fp32) return set_error("gemm: accumulate requires fp32 output");
-  const int nsm = num_sms();
+  const int nsm = (a.max_ctas > 0 && a.max_ctas < num_sms()) ? a.max_ctas : num_sms();  // SMs this launch may fill
   const int tiles_m = (a.M + BM - 1) / BM;
   const int total_kb = (a.K + BK - 1) / BK;
   // Tile width: model each CTA's time as (k-blocks it runs) x (BN + 64 columns of fixed per-k-block cost) plus a per-tile
@@ -484,8 +515,9 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   p.bias = a.bias; p.relu = a.relu;
   p.resid = reinterpret_cast<const __nv_bfloat16*>(a.resid); p.ldr = a.ldr; p.resid_op = a.resid ? a.resid_op : 0;
   p.alpha = a.alpha;
-  p.trace = g_gemm_trace;
+  p.trace = g_gemm_trace ? g_gemm_trace + size_t(g_gemm_trace_next++ % g_gemm_trace_slots) * (148 * 8) : nullptr;
   p.drop = a.drop;
+  p.b_static = a.b_static;
 
   CUtensorMap ta, tb;
   int rc;
@@ -515,7 +547,9 @@ int tensor_map_2d(const void* ptr, unsigned long long inner, unsigned long long 
   return get_tmap(ptr, inner, outer, ld, box_outer, static_cast<CUtensorMap*>(out_cu_tensor_map), kind);
 }
 
-void gemm_set_trace(unsigned long long* dev_ptr) { g_gemm_trace = dev_ptr; }
+void gemm_set_trace(unsigned long long* dev_ptr, int slots) {
+  g_gemm_trace = dev_ptr; g_gemm_trace_slots = slots > 0 ? slots : 1; g_gemm_trace_next = 0;
+}
 
 void gemm_clear_tensor_map_cache() {
   std::lock_guard<std::mutex> lock(g_map_mutex);

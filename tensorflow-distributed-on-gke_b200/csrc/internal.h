@@ -20,16 +20,20 @@ void count_launch(int n = 1);
 long long launches_total();
 
 bool pdl_enabled();  // B200XF_PDL=0 switches programmatic dependent launch off
+int stream_priority(cudaStream_t stream);  // cached cudaStreamGetPriority
 
 // Launch with the programmatic-stream-serialization attribute (see ptx.cuh: pdl_wait / pdl_trigger).
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
-  cfg.attrs = attr; cfg.numAttrs = 1;
+  // the stream's priority, stated on the launch itself so that it is certainly part of a captured graph's kernel node
+  attr[1].id = cudaLaunchAttributePriority;
+  attr[1].val.priority = stream_priority(stream);
+  cfg.attrs = attr; cfg.numAttrs = 2;
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 
@@ -58,6 +62,8 @@ struct GemmArgs {
   float alpha = 1.f;
   int force_bn = 0;
   int no_tma_store = 0;  // debug: force the direct-store epilogue
+  int max_ctas = 0;      // cap on the persistent grid (0 = every SM)
+  int b_static = 0;      // B (weights) is not written by the kernel launched just before: prefetch it ahead of the dependency wait
   DropArgs drop;         // inverted dropout on (acc + bias) before the residual add (transformer_model.py:196,202,232,238,244)
 };
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream);
@@ -66,7 +72,9 @@ void gemm_clear_tensor_map_cache();
 // 32-column box; `out_cu_tensor_map` points at a CUtensorMap.
 int tensor_map_2d(const void* ptr, unsigned long long inner, unsigned long long outer, unsigned long long ld, unsigned box_outer,
                   void* out_cu_tensor_map, int kind);
-void gemm_set_trace(unsigned long long* dev_ptr);  // debug: per-CTA phase time stamps (8 x u64 per CTA), null to disable
+// debug: per-CTA phase time stamps (8 x u64 per CTA, 148 CTAs per slot); successive launches use successive slots of
+// the ring (stamps are baked into a captured graph, so a replayed step fills its slots again); null to disable
+void gemm_set_trace(unsigned long long* dev_ptr, int slots = 1);
 
 // ---- attention (fused, masks derived in-tile from token ids; transformer_model.py:73-109,350-363)
 struct AttnArgs {
