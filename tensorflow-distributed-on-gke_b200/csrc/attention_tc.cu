@@ -35,6 +35,7 @@ struct TcArgs {
   bf16* o; int ldo; float* lse;   // forward only
   int H, Sq, Sk, causal;
   float scale, scale_log2;
+  int early;   // bit 0: q, bit 1: k and v are not outputs of the kernel launched just before -> loaded ahead of the dependency wait
 };
 
 // smem: sQ sK sV sdO (16 KB each) | sP (32 KB) | sdS (32 KB) | barriers
@@ -82,6 +83,13 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     ptx::prefetch_tmap(&tm_q); ptx::prefetch_tmap(&tm_k); ptx::prefetch_tmap(&tm_v); ptx::prefetch_tmap(&tm_do);
     ptx::mbar_init(&bars[0], 1); ptx::mbar_init(&bars[1], 1); ptx::mbar_init(&bars[2], 256); ptx::mbar_init(&bars[3], 1);
     ptx::fence_barrier_init();
+    ptx::mbar_expect_tx(&bars[0], 4 * kTileBytes);
+    // saved forward activations can be on their way while the kernel that produces dO is still finishing
+    if (p.early & 1) ptx::tma_load_2d(sQ, &tm_q, &bars[0], h * kD, b * p.Sq);
+    if (p.early & 2) {
+      ptx::tma_load_2d(sK, &tm_k, &bars[0], h * kD, b * p.Sk);
+      ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
+    }
   }
   if (warp == 1) { ptx::tmem_alloc(tmem_slot, 512); ptx::tmem_relinquish(); }
   pdl_wait();   // everything above overlaps the tail of the previous kernel
@@ -98,11 +106,12 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
 
   if (warp == 0) {
     if (lane == 0) {
-      ptx::mbar_expect_tx(&bars[0], 4 * kTileBytes);
-      ptx::tma_load_2d(sQ, &tm_q, &bars[0], h * kD, b * p.Sq);
+      if (!(p.early & 1)) ptx::tma_load_2d(sQ, &tm_q, &bars[0], h * kD, b * p.Sq);
       ptx::tma_load_2d(sdO, &tm_do, &bars[0], h * kD, b * p.Sq);
-      ptx::tma_load_2d(sK, &tm_k, &bars[0], h * kD, b * p.Sk);
-      ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
+      if (!(p.early & 2)) {
+        ptx::tma_load_2d(sK, &tm_k, &bars[0], h * kD, b * p.Sk);
+        ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
+      }
       ptx::mbar_wait(&bars[0], 0);
       ptx::tc_fence_after();
       // S = Q K^T, dP = dO V^T : A, B K-major, 4 k-steps of 16 over the head dimension
@@ -238,6 +247,12 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     ptx::prefetch_tmap(&tm_q); ptx::prefetch_tmap(&tm_k); ptx::prefetch_tmap(&tm_v);
     ptx::mbar_init(&bars[0], 1); ptx::mbar_init(&bars[1], 1); ptx::mbar_init(&bars[2], 128); ptx::mbar_init(&bars[3], 1);
     ptx::fence_barrier_init();
+    ptx::mbar_expect_tx(&bars[0], 3 * kTileBytes);
+    if (p.early & 1) ptx::tma_load_2d(sQ, &tm_q, &bars[0], h * kD, b * p.Sq);
+    if (p.early & 2) {  // cross-attention: K and V of every layer were projected right after the encoder
+      ptx::tma_load_2d(sK, &tm_k, &bars[0], h * kD, b * p.Sk);
+      ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
+    }
   }
   if (warp == 1) { ptx::tmem_alloc(tmem_slot, 256); ptx::tmem_relinquish(); }
   pdl_wait();
@@ -254,10 +269,11 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
 
   if (warp == 0) {
     if (lane == 0) {
-      ptx::mbar_expect_tx(&bars[0], 3 * kTileBytes);
-      ptx::tma_load_2d(sQ, &tm_q, &bars[0], h * kD, b * p.Sq);
-      ptx::tma_load_2d(sK, &tm_k, &bars[0], h * kD, b * p.Sk);
-      ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
+      if (!(p.early & 1)) ptx::tma_load_2d(sQ, &tm_q, &bars[0], h * kD, b * p.Sq);
+      if (!(p.early & 2)) {
+        ptx::tma_load_2d(sK, &tm_k, &bars[0], h * kD, b * p.Sk);
+        ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
+      }
       ptx::mbar_wait(&bars[0], 0);
       ptx::tc_fence_after();
       constexpr uint32_t idesc_kk = ptx::make_idesc_bf16(128, 128, 0, 0);
@@ -815,6 +831,7 @@ int attention_fwd_tc(const AttnArgs& a, cudaStream_t stream) {
   p.key_tokens = a.key_tokens; p.o = a.o; p.ldo = a.ldo; p.lse = a.lse;
   p.H = a.H; p.Sq = a.Sq; p.Sk = a.Sk; p.causal = a.causal;
   p.scale = 1.0f / sqrtf(float(a.dk)); p.scale_log2 = p.scale * kLog2e;
+  p.early = a.early;
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] { attr_err = cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemFwd); });
@@ -836,6 +853,7 @@ int attention_bwd_tc(const AttnArgs& a, cudaStream_t stream) {
   p.dq = a.dq; p.dk_out = a.dk_out; p.dv_out = a.dv_out; p.lddq = a.lddq; p.lddk = a.lddk; p.lddv = a.lddv;
   p.H = a.H; p.Sq = a.Sq; p.Sk = a.Sk; p.causal = a.causal;
   p.scale = 1.0f / sqrtf(float(a.dk)); p.scale_log2 = p.scale * kLog2e;
+  p.early = a.early;
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] { attr_err = cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBwd); });

@@ -348,7 +348,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   if (const char* e = getenv("B200XF_GRAPH")) use_graph = atoi(e) != 0;
   if (const char* e = getenv("B200XF_SHARDED_UPDATE")) sharded_update = atoi(e) != 0;
   if (const char* e = getenv("B200XF_BUCKET_JOIN")) bucket_join = atoi(e) != 0;
-  if (const char* e = getenv("B200XF_WEIGHT_PREFETCH")) weights_static = atoi(e) != 0 ? 1 : 0;
+  if (const char* e = getenv("B200XF_WEIGHT_PREFETCH")) weights_static = atoi(e);  // bit mask, see context.h
   if (const char* e = getenv("B200XF_BUCKET_MB")) { bucket_bytes = size_t(std::max(1, atoi(e))) << 20; bucket_bytes_set = true; }
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_ready, cudaEventDisableTiming));
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_done, cudaEventDisableTiming));
@@ -488,7 +488,7 @@ int Context::dense_fwd(const bf16* x, int M, const Dense& p, bf16* y, int relu, 
   g.bias = params + p.b; g.relu = relu;
   g.resid = resid; g.ldr = p.ld; g.resid_op = resid ? 1 : 0;
   if (drop_site >= 0) g.drop = site_drop(drop_site);
-  g.b_static = weights_static;
+  g.b_static = weights_static & 1;
   return gemm_bf16(g, stream);
 }
 int Context::dense_dgrad(const bf16* dy, int M, const Dense& p, bf16* dx, const bf16* resid, int resid_op) {
@@ -498,7 +498,7 @@ int Context::dense_dgrad(const bf16* dy, int M, const Dense& p, bf16* dx, const 
   g.d = dx; g.ldd = p.K; g.d_fp32 = 0;
   g.M = M; g.N = p.K; g.K = p.N;
   g.resid = resid; g.ldr = p.K; g.resid_op = resid ? resid_op : 0;
-  g.b_static = weights_static;
+  g.b_static = weights_static & 1;
   return gemm_bf16(g, stream);
 }
 int Context::dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p) {
@@ -509,6 +509,9 @@ int Context::dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p) {
   g.M = p.K; g.N = p.N; g.K = M;
   cudaStream_t s;
   B200XF_TRY(side_launch_begin(&s));
+  // No operand prefetch here: dy arrives over the fork event, and a launch with the programmatic attribute may begin
+  // before that event has fired (the dependency is resolved at griddepcontrol.wait) -- prefetching it read stale
+  // gradients; prefetching only x (a forward activation) measured slower.
   B200XF_TRY(gemm_bf16(g, s));
   return side_launch_end(dy);
 }
@@ -572,6 +575,7 @@ int Context::forward(const long long* inp, const long long* tgt_in, int B, int S
     c2.q = a.q2; c2.ldq = d; c2.k = kv + size_t(l) * 2 * d; c2.v = kv + size_t(l) * 2 * d + d; c2.ldk = c2.ldv = kv_all.ld;
     c2.o = a.ctx2; c2.ldo = d; c2.lse = a.lse2; c2.key_tokens = inp; c2.causal = 0;
     c2.B = B; c2.H = H; c2.Sq = T; c2.Sk = S; c2.dk = dk;
+    c2.early = (weights_static & 2) ? 2 : 0;  // K|V of all layers were projected right after the encoder
     B200XF_TRY(attention_fwd(c2, stream));
     B200XF_TRY(dense_fwd(a.ctx2, Nt, w.o2, a.z2, 0, a.o1, 3 + 2 * L + 3 * l));
     B200XF_TRY(layernorm_fwd(a.z2, nullptr, params + w.ln2.g, params + w.ln2.b, a.o2, nullptr, st + 2 * Nt, st + 3 * Nt, Nt, d, eps, stream));
@@ -696,6 +700,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     B200XF_TRY(sb_write(sb_dq2, &dq2));
     c2.d_o = dctx; c2.lddo = d; c2.dq = dq2; c2.lddq = d;
     c2.dk_out = dkv + size_t(l) * 2 * d; c2.dv_out = dkv + size_t(l) * 2 * d + d; c2.lddk = c2.lddv = kv_all.ld; c2.delta = delta; c2.dq_acc = dq_acc;
+    c2.early = (weights_static & 2) ? 3 : 0;
     B200XF_TRY(attention_bwd(c2, stream));
     B200XF_TRY(colsum(dq2, d, Nt, d, w.q2.b));
     B200XF_TRY(dense_wgrad(a.o1, dq2, Nt, w.q2));
@@ -712,6 +717,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     B200XF_TRY(sb_write(sb_dqkv, &dqkv));
     s1.d_o = dctx; s1.lddo = d; s1.dq = dqkv; s1.dk_out = dqkv + d; s1.dv_out = dqkv + 2 * d; s1.lddq = s1.lddk = s1.lddv = 3 * d;
     s1.delta = delta; s1.dq_acc = dq_acc;
+    s1.early = (weights_static & 2) ? 3 : 0;
     B200XF_TRY(attention_bwd(s1, stream));
     B200XF_TRY(colsum(dqkv, 3 * d, Nt, 3 * d, w.qkv1.b));
     B200XF_TRY(dense_wgrad(x, dqkv, Nt, w.qkv1));
@@ -748,6 +754,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     B200XF_TRY(sb_write(sb_dqkv, &dqkv));
     at.d_o = dctx; at.lddo = d; at.dq = dqkv; at.dk_out = dqkv + d; at.dv_out = dqkv + 2 * d; at.lddq = at.lddk = at.lddv = 3 * d;
     at.delta = delta; at.dq_acc = dq_acc;
+    at.early = (weights_static & 2) ? 3 : 0;
     B200XF_TRY(attention_bwd(at, stream));
     B200XF_TRY(colsum(dqkv, 3 * d, Ns, 3 * d, w.qkv.b));
     B200XF_TRY(dense_wgrad(x, dqkv, Ns, w.qkv));

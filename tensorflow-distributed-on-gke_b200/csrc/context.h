@@ -89,7 +89,10 @@ struct Context {
   bool sharded_update = true;
   // the bf16 weight copy is only written by the optimizer, never by the kernel just before a forward / data-gradient
   // GEMM on the compute stream, so those GEMMs may fetch their first weight tiles ahead of the dependency wait
-  int weights_static = 1;  // B200XF_WEIGHT_PREFETCH=0 disables
+  // Bit mask of the loads issued ahead of the dependency wait (B200XF_WEIGHT_PREFETCH): 1 weight tiles in forward /
+  // data-gradient GEMMs, 2 saved Q/K/V in the attention kernels (backward: all three; forward cross-attention: K, V).
+  // Measured and dropped: LayerNorm-backward saved state and the weight-gradient GEMM's activation operand (both slower).
+  int weights_static = 3;
   bool bucket_bytes_set = false;  // B200XF_BUCKET_MB given
   bool bucket_join = true;  // a closing bucket makes the compute stream wait for the side stream (B200XF_BUCKET_JOIN)
   bool overlap_update = false;

@@ -93,6 +93,9 @@ struct AttnArgs {
   bf16* dv_out = nullptr; int lddv = 0;
   float* delta = nullptr;                 // scratch [B,H,Sq]
   float* dq_acc = nullptr;                // optional scratch: fp32 [B*Sq, H*dk] dQ accumulator (enables the multi-tile tcgen05 backward)
+  // bit 0: q, bit 1: k and v are NOT outputs of the kernel launched just before this one on the stream (e.g. saved
+  // forward activations in the backward pass): the single-tile tcgen05 kernels fetch them ahead of the dependency wait
+  int early = 0;
 };
 int attention_fwd(const AttnArgs& a, cudaStream_t stream);
 int attention_bwd(const AttnArgs& a, cudaStream_t stream);
