@@ -143,6 +143,11 @@ int b200xf_gemm_bf16(const void* a, int lda, int a_mn, const void* b, int ldb, i
  * records %globaltimer stamps per CTA (start, set-up done, first operands landed, last MMA issued, accumulator ready,
  * epilogue done, exit).  Pass NULL to switch it off. */
 int b200xf_debug_gemm_trace(void* device_u64_buffer);
+/* CTA pairs (tcgen05 cta_group::2: the two SMs of a TPC share one 256-row tile and each stage only half of the B tile).
+ * mode -1 = heuristic (default: wide tiles with at least three waves of work), 0 = never, 1 = whenever M > 128 and the
+ * tile is at least 128 columns wide.  Process-wide; tests use it to run every shape through both kernels.
+ * No counterpart in the reference (tuning / test hook). */
+int b200xf_gemm_set_pair_mode(int mode);
 /* Same, for a whole step: the buffer holds `slots` x 148 x 8 u64 and successive launches use successive slots (wrapping).
  * Stamp 7 of a slot's first CTA is (M << 44 | N << 24 | K << 4 | a_mn << 1 | b_mn).  Launches captured into a CUDA graph
  * keep their slot, so replaying the step refills the ring.  No counterpart in the reference (debugging aid). */

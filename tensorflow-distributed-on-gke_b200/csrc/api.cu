@@ -153,6 +153,12 @@ int b200xf_debug_gemm_trace(void* device_u64_buffer) {
   return 0;
 }
 
+int b200xf_gemm_set_pair_mode(int mode) {
+  if (mode < -1 || mode > 1) return set_error("gemm pair mode must be -1 (heuristic), 0 (never) or 1 (always)");
+  gemm_set_pair_mode(mode);
+  return 0;
+}
+
 int b200xf_debug_gemm_trace_ring(void* device_u64_buffer, int slots) {
   if (device_u64_buffer && slots <= 0) return set_error("gemm trace ring: slots must be positive");
   gemm_set_trace(static_cast<unsigned long long*>(device_u64_buffer), slots);

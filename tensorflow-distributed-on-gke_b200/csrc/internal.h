@@ -37,6 +37,23 @@ inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 
+// Same, as thread-block clusters of `cluster_x` consecutive CTAs (grid.x must be a multiple of it).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k_cluster(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, int cluster_x,
+                                    Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[3];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  attr[1].id = cudaLaunchAttributePriority;
+  attr[1].val.priority = stream_priority(stream);
+  attr[2].id = cudaLaunchAttributeClusterDimension;
+  attr[2].val.clusterDim.x = cluster_x; attr[2].val.clusterDim.y = 1; attr[2].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = cluster_x > 1 ? 3 : 2;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 #define B200XF_CUDA(expr)                                                                          \
   do {                                                                                             \
     cudaError_t _e = (expr);                                                                       \
@@ -64,10 +81,12 @@ struct GemmArgs {
   int no_tma_store = 0;  // debug: force the direct-store epilogue
   int max_ctas = 0;      // cap on the persistent grid (0 = every SM)
   int b_static = 0;      // B (weights) is not written by the kernel launched just before: prefetch it ahead of the dependency wait
+  int pair = 0;          // CTA pairs (cta_group::2, 256-row tiles): 0 auto, 1 force when M >= 256, -1 never
   DropArgs drop;         // inverted dropout on (acc + bias) before the residual add (transformer_model.py:196,202,232,238,244)
 };
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream);
 void gemm_clear_tensor_map_cache();
+void gemm_set_pair_mode(int mode);  // CTA pairs: -1 heuristic (default), 0 never, 1 whenever M > 128 and the tile is >= 128 wide
 // Cached 2-D TMA descriptor (128B swizzle) of a row-major matrix: kind 0 = bf16 with a 64-column box, 1 = fp32 with a
 // 32-column box; `out_cu_tensor_map` points at a CUtensorMap.
 int tensor_map_2d(const void* ptr, unsigned long long inner, unsigned long long outer, unsigned long long ld, unsigned box_outer,

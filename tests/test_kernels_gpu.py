@@ -89,6 +89,46 @@ def test_gemm_wgrad_accumulate_split_k(split_k):
     assert _rel(acc, ref) < 2e-5
 
 
+@pytest.fixture
+def forced_pairs():
+    """Every eligible GEMM runs as CTA pairs (cta_group::2) inside the block; the heuristic is restored afterwards."""
+    lib = b200xf._lib.load()
+    b200xf._lib.check(lib.b200xf_gemm_set_pair_mode(1))
+    yield
+    b200xf._lib.check(lib.b200xf_gemm_set_pair_mode(-1))
+
+
+@pytest.mark.parametrize("layout", list(LAYOUTS))
+@pytest.mark.parametrize("shape", [(256, 256, 128), (300, 200, 136), (2560, 384, 128), (130, 7010, 128), (512, 520, 4096),
+                                   (2176, 1000, 512), (1024, 4096, 96)])
+@pytest.mark.parametrize("bn", [0, 128, 256])
+def test_gemm_cta_pairs(layout, shape, bn, forced_pairs):
+    # odd numbers of 128-row blocks (300, 130, 2176 rows: the last pair's second CTA is partly or wholly out of range),
+    # ragged N and K, one and many tiles per pair
+    test_gemm_layouts(layout, shape, bn)
+
+
+def test_gemm_cta_pairs_epilogues_and_split_k(forced_pairs):
+    test_gemm_epilogues()
+    for split_k in (0, 1, 3, 8):
+        test_gemm_wgrad_accumulate_split_k(split_k)
+
+
+def test_gemm_cta_pairs_heuristic_matches_single():
+    """The shapes the heuristic sends to CTA pairs (>= 3 waves of 256-wide tiles) agree with the single-CTA kernel."""
+    lib = b200xf._lib.load()
+    g = torch.Generator(device=DEV).manual_seed(5)
+    x = _bf(torch.randn(4096, 512, device=DEV, generator=g)); w = _bf(torch.randn(512, 8192, device=DEV, generator=g) * 0.05)
+    bias = torch.randn(8192, device=DEV, generator=g)
+    try:
+        b200xf._lib.check(lib.b200xf_gemm_set_pair_mode(0)); single = K.gemm(x, w, b_mn=True, bias=bias)
+        b200xf._lib.check(lib.b200xf_gemm_set_pair_mode(-1)); auto = K.gemm(x, w, b_mn=True, bias=bias)
+    finally:
+        b200xf._lib.check(lib.b200xf_gemm_set_pair_mode(-1))
+    torch.cuda.synchronize()
+    assert torch.equal(single, auto)  # same products, same k order, same rounding
+
+
 # ------------------------------------------------------------------------------------------ attention
 def _attn_ref(q, k, v, key_tokens, causal, H):
     """transformer_model.py:73-109 + masks :56-70,:350-363, in fp32."""
