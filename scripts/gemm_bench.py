@@ -34,10 +34,21 @@ def bench(M, N, Kd, lay, bn=0, split_k=0, reps=20):
 
 if __name__ == "__main__":
     d, dff, V, tok = 512, 2048, 32000, 4096
-    cases = [(tok, 3 * d, d, "fwd"), (tok, d, d, "fwd"), (tok, dff, d, "fwd"), (tok, d, dff, "fwd"), (tok, V, d, "fwd"),
+    cases = [(tok, 3 * d, d, "fwd"), (tok, d, d, "fwd"), (tok, dff, d, "fwd"), (tok, d, dff, "fwd"), (tok, 12 * d, d, "fwd"), (tok, V, d, "fwd"),
              (tok, d, 3 * d, "dgrad"), (tok, d, d, "dgrad"), (tok, d, dff, "dgrad"), (tok, dff, d, "dgrad"), (tok, d, V, "dgrad"),
              (d, 3 * d, tok, "wgrad"), (d, d, tok, "wgrad"), (d, dff, tok, "wgrad"), (dff, d, tok, "wgrad"), (d, V, tok, "wgrad"),
              (8192, 8192, 8192, "dgrad"), (8192, 8192, 8192, "fwd")]
+    lib = b200xf._lib.load()
+    if "--pairs" in sys.argv:  # single-CTA kernel vs CTA pairs (cta_group::2) vs the heuristic
+        for M, N, Kd, lay in cases:
+            cols = []
+            for mode, bn, tag in ((0, 0, "single auto"), (1, 128, "pair bn128"), (1, 256, "pair bn256"), (-1, 0, "heuristic")):
+                lib.b200xf_gemm_set_pair_mode(mode)
+                us, tf = bench(M, N, Kd, lay, bn)
+                cols.append(f"{tag}: {us:7.1f} us {tf:7.1f} TF")
+            lib.b200xf_gemm_set_pair_mode(-1)
+            print(f"{lay:6s} M={M:5d} N={N:5d} K={Kd:5d} | " + " | ".join(cols), flush=True)
+        sys.exit(0)
     for M, N, Kd, lay in cases:
         res = []
         for bn in (64, 128, 256):

@@ -43,7 +43,7 @@ struct Cfg {
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = (PAIR ? BN / 2 : BN) * BK * 2;  // per CTA
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (kStageBytes > 32768) ? 4 : 6;
+  static constexpr int kStages = (192 * 1024 / kStageBytes) > 8 ? 8 : (192 * 1024 / kStageBytes);  // 48 KB: 4, 32 KB: 6, 24 KB: 8
   static constexpr int kSmem = kStages * kStageBytes + 4 * 2 * 4096 /*store staging*/ + 1024 /*bias slice*/ + 1024 /*align slack*/ + 256 /*barriers*/;
   static constexpr int kTmemCols = 2 * BN;  // double-buffered accumulator
 };
@@ -531,16 +531,20 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
       if (best < 0 || cost < best) { best = cost; bn = cand; }
     }
   }
+  // CTA pairs: 256-row tiles worked by the two SMs of a TPC (needs two 128-row blocks and a B half of >= 64 columns).
+  // Measured against the single-CTA kernel (scripts/gemm_bench.py --pairs): 256-wide pair tiles gain 14-18% on the
+  // vocabulary and K|V projections and reach 1.43 PFLOP/s at 8192^3; back to back they also gain 3-8% on the one-to-
+  // two-wave QKV / FFN1 GEMMs, but inside the step those lose it again (a pair needs both SMs of a TPC free at once, and
+  // cluster scheduling plus the pair's extra synchronisation are fixed costs: 4.08 ms/step with them, 4.02 without), and
+  // single-wave problems lose 10-20%; 128-wide pair tiles always lose.  Hence: at least three waves of 256-wide tiles.
+  const long wide_tiles = long(tiles_m) * ((a.N + 255) / 256);
+  const bool pair_auto = a.N > 256 && wide_tiles >= 3L * nsm;
+  if (a.force_bn == 0 && a.pair >= 0 && pair_mode() < 0 && pair_auto && a.M > BM && nsm >= 2) bn = 256;
   if (bn != 64 && bn != 128 && bn != 256) return set_error("gemm: unsupported BN %d", bn);
   const int tiles_n = (a.N + bn - 1) / bn;
   plan(bn, &splits);
-  // CTA pairs: 256-row tiles worked by the two SMs of a TPC (needs two 128-row blocks and a B half of >= 64 columns)
-  // Measured: +15-18% on the multi-wave GEMMs (vocabulary projection forward / weight gradient, 8192^3 reaches the
-  // 1.4 PFLOP/s sustained peak), -15% on single-wave ones (cluster scheduling and the pair's extra synchronisation are
-  // fixed costs) -> by default only wide tiles with at least three waves of work.
   const bool pair_ok = a.pair >= 0 && bn >= 128 && a.M > BM && nsm >= 2;
-  const bool pair_auto = bn == 256 && long(tiles_m) * tiles_n * splits >= 3L * nsm;
-  const bool pair = pair_ok && (a.pair > 0 || pair_mode() == 1 || (pair_mode() < 0 && pair_auto));
+  const bool pair = pair_ok && (a.pair > 0 || pair_mode() == 1 || (pair_mode() < 0 && pair_auto && bn == 256));
   int tiles_m_eff = tiles_m;
   if (pair) {
     tiles_m_eff = (a.M + 2 * BM - 1) / (2 * BM);
