@@ -503,15 +503,26 @@ int prep_targets(const long long* target, long long* tgt_in, long long* labels, 
 namespace {
 constexpr int kCeThreads = 256;
 
+// 2^x for x <= 0 as the bare MUFU instruction: exp2f() wraps it in a range test and two scalings for arguments whose
+// result would be denormal; here such results are flushed to zero (they are below 1e-38 of the row maximum's weight).
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 struct MaxSum { float m, s; };
 __device__ __forceinline__ MaxSum combine(MaxSum a, MaxSum b) {
   const float m = fmaxf(a.m, b.m);
   if (m == -INFINITY) return {m, 0.f};
-  return {m, a.s * exp2f((a.m - m) * 1.4426950408889634f) + b.s * exp2f((b.m - m) * 1.4426950408889634f)};
+  return {m, a.s * fast_exp2((a.m - m) * 1.4426950408889634f) + b.s * fast_exp2((b.m - m) * 1.4426950408889634f)};
 }
 
 // One block per target position: pass 1 = online max/sum-exp, first-max argmax, label logit;
 // pass 2 (row now L2-resident) = dlogits = (softmax - onehot) * mask / (count * workers), in place.
+constexpr float kLog2eCe = 1.4426950408889634f;
+
+constexpr int kCeUnroll = 4;
 __global__ void __launch_bounds__(kCeThreads)
 vocab_ce_kernel(bf16* __restrict__ logits, int ldl, const long long* __restrict__ labels, int V,
                 const int* __restrict__ nonpad_count, float inv_workers, float* __restrict__ row_loss,
@@ -535,24 +546,40 @@ vocab_ce_kernel(bf16* __restrict__ logits, int ldl, const long long* __restrict_
     if (threadIdx.x == 0) { row_loss[row] = 0.f; row_correct[row] = 0; }
     return;
   }
+  // running (max, sum of 2^((x - max) log2 e)) per thread: the sum is rescaled only when the maximum moves, which after
+  // the first few vectors is rare -- one MUFU per logit instead of 1.25
   MaxSum ms{-INFINITY, 0.f};
   float am = -INFINITY; int ai = 0x7fffffff;
-  for (int i = threadIdx.x; i < nvec; i += kCeThreads) {
-    float f[8];
-    if (i * 8 + 8 <= V) unpack8(*reinterpret_cast<const uint4*>(x + i * 8), f);
-    else for (int j = 0; j < 8; ++j) f[j] = (i * 8 + j < V) ? __bfloat162float(x[i * 8 + j]) : -INFINITY;
-    float lm = f[0];
+  float mneg = 0.f;  // -max * log2(e), kept ready for the FMA below
+  // kCeUnroll independent 16-byte loads per thread and iteration: one load in flight per thread (32 KB per SM) cannot
+  // cover HBM latency at more than ~2.5 TB/s
+  for (int i0 = threadIdx.x; i0 < nvec; i0 += kCeThreads * kCeUnroll) {
+    uint4 u[kCeUnroll];
 #pragma unroll
-    for (int j = 1; j < 8; ++j) lm = fmaxf(lm, f[j]);
-    if (lm > am) {  // strictly greater keeps the earliest index within this thread's ascending scan
-#pragma unroll
-      for (int j = 7; j >= 0; --j) if (f[j] == lm) ai = i * 8 + j;
-      am = lm;
+    for (int k = 0; k < kCeUnroll; ++k) {
+      const int i = i0 + k * kCeThreads;
+      if (i < nvec && i * 8 + 8 <= V) u[k] = *reinterpret_cast<const uint4*>(x + i * 8);
     }
-    float ls = 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) ls += exp2f((f[j] - lm) * 1.4426950408889634f);
-    ms = combine(ms, MaxSum{lm, ls});
+    for (int k = 0; k < kCeUnroll; ++k) {
+      const int i = i0 + k * kCeThreads;
+      if (i >= nvec) break;
+      float f[8];
+      if (i * 8 + 8 <= V) unpack8(u[k], f);
+      else for (int j = 0; j < 8; ++j) f[j] = (i * 8 + j < V) ? __bfloat162float(x[i * 8 + j]) : -INFINITY;
+      float lm = f[0];
+#pragma unroll
+      for (int j = 1; j < 8; ++j) lm = fmaxf(lm, f[j]);
+      if (lm > am) {  // strictly greater keeps the earliest index within this thread's ascending scan
+#pragma unroll
+        for (int j = 7; j >= 0; --j) if (f[j] == lm) ai = i * 8 + j;
+        am = lm;
+        ms.s *= fast_exp2((ms.m - lm) * kLog2eCe);  // 2^(-inf) = 0 the first time
+        ms.m = lm; mneg = -lm * kLog2eCe;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ms.s += fast_exp2(fmaf(f[j], kLog2eCe, mneg));
+    }
   }
   // warp then block reduction
 #pragma unroll
@@ -584,18 +611,31 @@ vocab_ce_kernel(bf16* __restrict__ logits, int ldl, const long long* __restrict_
   __syncthreads();
   const float mx = bc[0], inv_s = bc[1], scale = bc[2];
   const int lab = bci;
-  for (int i = threadIdx.x; i < nvec; i += kCeThreads) {
-    float f[8];
-    const bool fullv = i * 8 + 8 <= V;
-    if (fullv) unpack8(*reinterpret_cast<const uint4*>(x + i * 8), f);
-    else for (int j = 0; j < 8; ++j) f[j] = (i * 8 + j < V) ? __bfloat162float(x[i * 8 + j]) : -INFINITY;
+  const float mxneg = -mx * kLog2eCe, ps = inv_s * scale;
+  for (int i0 = threadIdx.x; i0 < nvec; i0 += kCeThreads * kCeUnroll) {
+    uint4 u[kCeUnroll];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float pr = exp2f((f[j] - mx) * 1.4426950408889634f) * inv_s;
-      f[j] = (pr - ((i * 8 + j == lab) ? 1.f : 0.f)) * scale;
+    for (int k = 0; k < kCeUnroll; ++k) {
+      const int i = i0 + k * kCeThreads;
+      if (i < nvec && i * 8 + 8 <= V) u[k] = *reinterpret_cast<const uint4*>(x + i * 8);
     }
-    if (fullv) *reinterpret_cast<uint4*>(x + i * 8) = pack8(f);
-    else for (int j = 0; j < 8; ++j) if (i * 8 + j < V) x[i * 8 + j] = __float2bfloat16(f[j]);
+#pragma unroll
+    for (int k = 0; k < kCeUnroll; ++k) {
+      const int i = i0 + k * kCeThreads;
+      if (i >= nvec) break;
+      float f[8];
+      const bool fullv = i * 8 + 8 <= V;
+      if (fullv) unpack8(u[k], f);
+      else for (int j = 0; j < 8; ++j) f[j] = (i * 8 + j < V) ? __bfloat162float(x[i * 8 + j]) : -INFINITY;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = fast_exp2(fmaf(f[j], kLog2eCe, mxneg)) * ps;   // softmax * mask / (count * workers)
+      if ((lab >> 3) == i) {  // the label's vector (lab = -1 never matches): subtract the one-hot term
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if (j == (lab & 7)) f[j] -= scale;
+      }
+      if (fullv) *reinterpret_cast<uint4*>(x + i * 8) = pack8(f);
+      else for (int j = 0; j < 8; ++j) if (i * 8 + j < V) x[i * 8 + j] = __float2bfloat16(f[j]);
+    }
   }
 }
 
