@@ -348,6 +348,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   if (const char* e = getenv("B200XF_GRAPH")) use_graph = atoi(e) != 0;
   if (const char* e = getenv("B200XF_SHARDED_UPDATE")) sharded_update = atoi(e) != 0;
   if (const char* e = getenv("B200XF_BUCKET_JOIN")) bucket_join = atoi(e) != 0;
+  if (const char* e = getenv("B200XF_COMM_SMS")) comm_sms = std::max(0, atoi(e));
   if (const char* e = getenv("B200XF_WEIGHT_PREFETCH")) weights_static = atoi(e);  // bit mask, see context.h
   if (const char* e = getenv("B200XF_BUCKET_MB")) { bucket_bytes = size_t(std::max(1, atoi(e))) << 20; bucket_bytes_set = true; }
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_ready, cudaEventDisableTiming));
@@ -479,6 +480,14 @@ int Context::join_side() {
 }
 
 // ------------------------------------------------------------------------------------ GEMM helpers
+// With a communicator attached, NCCL's reduce-scatter / all-gather kernels sit on a few SMs for much of the backward
+// pass; a persistent GEMM grid that counts on all 148 SMs then waits for them with its last CTAs.  Leaving those SMs
+// out of the backward GEMM grids costs the 128-tile problems nothing.
+int Context::backward_gemm_cap() const {
+  if (!comm || world <= 1 || comm_sms <= 0) return 0;
+  return std::max(num_sms() / 2, num_sms() - comm_sms);
+}
+
 int Context::dense_fwd(const bf16* x, int M, const Dense& p, bf16* y, int relu, const bf16* resid, int drop_site) {
   GemmArgs g;
   g.a = x; g.lda = p.K; g.a_mn = 0;
@@ -499,6 +508,7 @@ int Context::dense_dgrad(const bf16* dy, int M, const Dense& p, bf16* dx, const 
   g.M = M; g.N = p.K; g.K = p.N;
   g.resid = resid; g.ldr = p.K; g.resid_op = resid ? resid_op : 0;
   g.b_static = weights_static & 1;
+  g.max_ctas = backward_gemm_cap();
   return gemm_bf16(g, stream);
 }
 int Context::dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p) {
@@ -507,6 +517,7 @@ int Context::dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p) {
   g.b = dy; g.ldb = p.ld; g.b_mn = 1;  // dY [tokens][N] == B stored [contract][N]
   g.d = grads + p.w; g.ldd = p.ld; g.d_fp32 = 1; g.accumulate = 1;
   g.M = p.K; g.N = p.N; g.K = M;
+  g.max_ctas = backward_gemm_cap();
   cudaStream_t s;
   B200XF_TRY(side_launch_begin(&s));
   // No operand prefetch here: dy arrives over the fork event, and a launch with the programmatic attribute may begin

@@ -93,6 +93,8 @@ struct Context {
   // data-gradient GEMMs, 2 saved Q/K/V in the attention kernels (backward: all three; forward cross-attention: K, V).
   // Measured and dropped: LayerNorm-backward saved state and the weight-gradient GEMM's activation operand (both slower).
   int weights_static = 3;
+  int comm_sms = 0;  // SMs left to the collectives' kernels during backward (B200XF_COMM_SMS); 0 = GEMMs use every SM
+  int backward_gemm_cap() const;
   bool bucket_bytes_set = false;  // B200XF_BUCKET_MB given
   bool bucket_join = true;  // a closing bucket makes the compute stream wait for the side stream (B200XF_BUCKET_JOIN)
   bool overlap_update = false;

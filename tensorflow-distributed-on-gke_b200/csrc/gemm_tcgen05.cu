@@ -61,7 +61,9 @@ struct GemmParams {
 };
 
 // bias add, ReLU, residual add / ReLU mask on 32 accumulator columns [col0, col0+32) of one output row.
-__device__ __forceinline__ void epilogue_math(float* f, const GemmParams& p, int row, bool row_ok, int col0, const float* sbias) {
+// `rpre`: the four 16-byte residual vectors of these 32 columns, already loaded (or null: load them here).
+__device__ __forceinline__ void epilogue_math(float* f, const GemmParams& p, int row, bool row_ok, int col0, const float* sbias,
+                                              const uint4* rpre = nullptr) {
   if (sbias) {  // this tile's bias slice, staged in shared memory once per tile (zero past N): broadcast reads
 #pragma unroll
     for (int j = 0; j < 32; j += 4) {
@@ -84,8 +86,8 @@ __device__ __forceinline__ void epilogue_math(float* f, const GemmParams& p, int
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       float r[8];
-      if (col0 + g * 8 + 8 <= p.N) {
-        const uint4 u = *reinterpret_cast<const uint4*>(rp + g * 8);
+      if (rpre != nullptr || col0 + g * 8 + 8 <= p.N) {
+        const uint4 u = rpre != nullptr ? rpre[g] : *reinterpret_cast<const uint4*>(rp + g * 8);
         r[0] = ptx::bf16_lo(u.x); r[1] = ptx::bf16_hi(u.x); r[2] = ptx::bf16_lo(u.y); r[3] = ptx::bf16_hi(u.y);
         r[4] = ptx::bf16_lo(u.z); r[5] = ptx::bf16_hi(u.z); r[6] = ptx::bf16_lo(u.w); r[7] = ptx::bf16_hi(u.w);
       } else {
@@ -284,11 +286,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const int tn = (t / p.tiles_m) % p.tiles_n, z = t / (p.tiles_m * p.tiles_n);
       const int tm = PAIR ? (t % p.tiles_m) * 2 + rank : t % p.tiles_m;  // this CTA's 128-row block
       const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
+      const int row = tm * BM + quarter * 32 + lane;
+      const bool row_ok = row < p.M;
+      // the residual of this thread's first 64 columns is requested before the accumulator is ready, so that its L2
+      // latency (0.6-0.8 us) runs under the main loop instead of inside the epilogue
+      uint4 rpre[8];
+      bool rpre_ok = false;
+      if (p.resid_op && p.d_tma && !p.d_fp32) {
+        const int c_first = (kChunksPerHalf >= 2) ? halfsel * kChunksPerHalf : (halfsel ? BN / 32 : 0);
+        const int colfirst = tn * BN + c_first * 32;
+        if (row_ok && c_first < BN / 32 && colfirst + 64 <= p.N) {
+          const uint4* rp = reinterpret_cast<const uint4*>(p.resid + size_t(row) * p.ldr + colfirst);
+#pragma unroll
+          for (int g = 0; g < 8; ++g) rpre[g] = rp[g];
+          rpre_ok = true;
+        }
+      }
       ptx::mbar_wait(&tmem_full[as], aph);
       ptx::tc_fence_after();
       if (it == 0 && warp == 2 && lane == 0) stamp(p, 4);
-      const int row = tm * BM + quarter * 32 + lane;
-      const bool row_ok = row < p.M;
       const uint32_t taddr = tmem_base + as * BN + (uint32_t(quarter * 32) << 16);
       const bool add_bias = p.bias != nullptr && z == 0;
       if (add_bias) {  // CTA-uniform: the four epilogue warps stage this tile's BN bias values once
@@ -326,7 +342,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
             float f[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
-            if (col0 < p.N) epilogue_math(f, p, row, row_ok, col0, add_bias ? sbias + (c0 + cc) * 32 : nullptr);
+            if (col0 < p.N) epilogue_math(f, p, row, row_ok, col0, add_bias ? sbias + (c0 + cc) * 32 : nullptr,
+                                          (rpre_ok && c0 == c_begin) ? rpre + cc * 4 : nullptr);
             if (p.d_fp32) {
 #pragma unroll
               for (int q = 0; q < 8; ++q)  // 8 x 16-byte chunks per 128-byte row, XOR-swizzled by the row index
