@@ -174,7 +174,7 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     mx = fmaxf(xch[i], xch[kT + i]);              // finite: key 0 always exists
     float sum = 0.f;
 #pragma unroll
-    for (int j = 0; j < 64; ++j) { s[j] = exp2f(s[j] - mx); sum += s[j]; }
+    for (int j = 0; j < 64; ++j) { s[j] = ptx::fast_exp2(s[j] - mx); sum += s[j]; }
     xch[2 * kT + half * kT + i] = sum;
     asm volatile("bar.sync 1, 256;" ::: "memory");
     sum = xch[2 * kT + i] + xch[3 * kT + i];
@@ -316,7 +316,7 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     }
     float sum = 0.f;
 #pragma unroll
-    for (int j = 0; j < kT; ++j) { s[j] = exp2f(s[j] - mx); sum += s[j]; }
+    for (int j = 0; j < kT; ++j) { s[j] = ptx::fast_exp2(s[j] - mx); sum += s[j]; }
 #pragma unroll
     for (int c = 0; c < 4; ++c) store_row32(sP, i, c * 32, s + c * 32);
     ptx::tc_fence_before();
@@ -469,10 +469,10 @@ attn_fwd_tc_multi_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
       x_max[half * kT + i] = mx;
       asm volatile("bar.sync 1, 256;" ::: "memory");
       const float m_new = fmaxf(m, fmaxf(x_max[i], x_max[kT + i]));   // finite: the first tile always holds a real key
-      const float corr = exp2f(m - m_new);
+      const float corr = ptx::fast_exp2(m - m_new);
       float sum = 0.f;
 #pragma unroll
-      for (int t = 0; t < 64; ++t) { s[t] = exp2f(s[t] - m_new); sum += s[t]; }
+      for (int t = 0; t < 64; ++t) { s[t] = ptx::fast_exp2(s[t] - m_new); sum += s[t]; }
       x_sum[half * kT + i] = sum;
       store_row32(sP, i, half * 64, s);
       store_row32(sP, i, half * 64 + 32, s + 32);
@@ -651,7 +651,7 @@ attn_bwd_tc_multi_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
           const int mk = s_mask[key];
           float v = sv[j] * p.scale_log2;
           if (mk == 1 || (p.causal && k0 + key > q0 + i)) v = kMasked;
-          const float pr = (mk == 2) ? 0.f : exp2f((v - m_cur) - l_cur);
+          const float pr = (mk == 2) ? 0.f : ptx::fast_exp2((v - m_cur) - l_cur);
           sv[j] = pr;
           dp[j] = pr * (dp[j] - d_cur);
         }

@@ -503,13 +503,7 @@ int prep_targets(const long long* target, long long* tgt_in, long long* labels, 
 namespace {
 constexpr int kCeThreads = 256;
 
-// 2^x for x <= 0 as the bare MUFU instruction: exp2f() wraps it in a range test and two scalings for arguments whose
-// result would be denormal; here such results are flushed to zero (they are below 1e-38 of the row maximum's weight).
-__device__ __forceinline__ float fast_exp2(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
+using ptx::fast_exp2;
 
 struct MaxSum { float m, s; };
 __device__ __forceinline__ MaxSum combine(MaxSum a, MaxSum b) {

@@ -177,6 +177,13 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int m, int n, int a_mn_ma
 }
 
 // ---------------------------------------------------------------- misc
+// 2^x as the bare MUFU instruction (2 ulp).  exp2f() wraps it in a range test and two scalings so that results below
+// 2^-126 come out as denormals; the softmax kernels only ever need such results to be (nearly) zero.
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
