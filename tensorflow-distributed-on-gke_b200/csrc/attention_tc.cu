@@ -94,6 +94,14 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
   if (warp == 1) { ptx::tmem_alloc(tmem_slot, 512); ptx::tmem_relinquish(); }
   pdl_wait();   // everything above overlaps the tail of the previous kernel
   pdl_trigger();
+  if (warp == 0 && lane == 0) {  // the rest of the operands, before anything else can delay them
+    if (!(p.early & 1)) ptx::tma_load_2d(sQ, &tm_q, &bars[0], h * kD, b * p.Sq);
+    ptx::tma_load_2d(sdO, &tm_do, &bars[0], h * kD, b * p.Sq);
+    if (!(p.early & 2)) {
+      ptx::tma_load_2d(sK, &tm_k, &bars[0], h * kD, b * p.Sk);
+      ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
+    }
+  }
   if (warp >= 2 && warp < 6) {
     const int j = threadIdx.x - 64;
     s_mask[j] = (j >= p.Sk) ? 2 : (p.key_tokens[size_t(b) * p.Sk + j] == 0 ? 1 : 0);
@@ -106,12 +114,6 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
 
   if (warp == 0) {
     if (lane == 0) {
-      if (!(p.early & 1)) ptx::tma_load_2d(sQ, &tm_q, &bars[0], h * kD, b * p.Sq);
-      ptx::tma_load_2d(sdO, &tm_do, &bars[0], h * kD, b * p.Sq);
-      if (!(p.early & 2)) {
-        ptx::tma_load_2d(sK, &tm_k, &bars[0], h * kD, b * p.Sk);
-        ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
-      }
       ptx::mbar_wait(&bars[0], 0);
       ptx::tc_fence_after();
       // S = Q K^T, dP = dO V^T : A, B K-major, 4 k-steps of 16 over the head dimension
@@ -257,6 +259,13 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
   if (warp == 1) { ptx::tmem_alloc(tmem_slot, 256); ptx::tmem_relinquish(); }
   pdl_wait();
   pdl_trigger();
+  if (warp == 0 && lane == 0) {  // the rest of the operands, before anything else can delay them
+    if (!(p.early & 1)) ptx::tma_load_2d(sQ, &tm_q, &bars[0], h * kD, b * p.Sq);
+    if (!(p.early & 2)) {
+      ptx::tma_load_2d(sK, &tm_k, &bars[0], h * kD, b * p.Sk);
+      ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
+    }
+  }
   if (warp >= 2) {
     const int j = threadIdx.x - 64;
     s_mask[j] = (j >= p.Sk) ? 2 : (p.key_tokens[size_t(b) * p.Sk + j] == 0 ? 1 : 0);
@@ -269,11 +278,6 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
 
   if (warp == 0) {
     if (lane == 0) {
-      if (!(p.early & 1)) ptx::tma_load_2d(sQ, &tm_q, &bars[0], h * kD, b * p.Sq);
-      if (!(p.early & 2)) {
-        ptx::tma_load_2d(sK, &tm_k, &bars[0], h * kD, b * p.Sk);
-        ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
-      }
       ptx::mbar_wait(&bars[0], 0);
       ptx::tc_fence_after();
       constexpr uint32_t idesc_kk = ptx::make_idesc_bf16(128, 128, 0, 0);
