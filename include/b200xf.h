@@ -85,6 +85,15 @@ int b200xf_attention_weights(b200xf_ctx* ctx, int decoder_layer, int block, floa
 /* tf.argmax(x, axis=-1) over fp32 DEVICE rows (tester.py:38): out[r] = lowest index of the maximum of row r. */
 int b200xf_argmax_rows(const float* x, int ld, int rows, int cols, int64_t* out, void* stream);
 
+/* On-device batch assembly: the `.to_tensor()` that ends the reference's tokenisation (english_portugese_dataset.py:36-39)
+ * pads the ragged sentences of a batch with 0 (PAD) to a common length, and experimental_distribute_dataset
+ * (__main__.py:48-53) hands each replica a contiguous slice of the rows.  flat_tokens: the batch's sentences back to back
+ * (DEVICE int64), offsets: [n_sentences + 1] DEVICE int64 (sentence r = flat[offsets[r], offsets[r+1])); writes rows
+ * first_row .. first_row + rows - 1 into out [rows, length] (DEVICE int64).  *too_long (DEVICE int, zeroed by the caller)
+ * receives the longest sentence length that did not fit `length` (such rows are truncated). */
+int b200xf_assemble_padded(const int64_t* flat_tokens, const int64_t* offsets, int first_row, int rows, int length, int64_t* out,
+                           int* too_long, void* stream);
+
 /* ---- train_step (__main__.py:105-117): shift, forward, local_loss_function(.., workers_count), backward,
  * gradient all-reduce when a communicator is attached (cluster/cluster.py:66), Adam + schedule in place,
  * accuracy counts.  inp [B,S], target [B,T+1] int64.  out6 (fp32) = {local loss (already / workers_count),

@@ -5,6 +5,8 @@ CUDA library (libb200xf.so, sm_100a).  No CPU fallback: without the built librar
 """
 from . import _lib
 from ._lib import B200XFError, LIB_PATH
+from .batching import BatchAssembler, pad_to_longest, padded_length, ragged_to_flat, replica_rows
+from .cluster import B200Cluster, launch
 from .synthetic import CONFIGS, step_flops, synthetic_batch
 from .training import (Adam, B200Strategy, CustomSchedule, Mean, ReduceOp, StepResult, TransformerLearningRateSchedule,
                        make_distributed_train_step, make_test_step, make_train_step)
@@ -16,4 +18,5 @@ __all__ = [
     "create_padding_mask", "create_look_ahead_mask", "TransformerLearningRateSchedule", "CustomSchedule", "Adam",
     "B200Strategy", "ReduceOp", "Mean", "StepResult", "make_train_step", "make_distributed_train_step", "make_test_step",
     "synthetic_batch", "step_flops", "CONFIGS", "B200XFError", "LIB_PATH",
+    "BatchAssembler", "pad_to_longest", "padded_length", "ragged_to_flat", "replica_rows", "B200Cluster", "launch",
 ]

@@ -66,6 +66,7 @@ SIGNATURES = {
     "b200xf_comm_destroy": (_I, [_P]),
     "b200xf_allreduce_bucket": (_I, [_P, _P, _L]),
     "b200xf_gemm_bf16": (_I, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _I, _I, _I, _P, _I, _P, _I, _I, _F, _I, _I, _P]),
+    "b200xf_assemble_padded": (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),
     "b200xf_debug_gemm_trace": (_I, [_P]),
     "b200xf_debug_gemm_trace_ring": (_I, [_P, _I]),
     "b200xf_gemm_set_pair_mode": (_I, [_I]),

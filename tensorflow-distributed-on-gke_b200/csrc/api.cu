@@ -111,6 +111,12 @@ int b200xf_argmax_rows(const float* x, int ld, int rows, int cols, int64_t* out,
   if (!x || !out) return set_error("null argument");
   return argmax_rows(x, ld, rows, cols, reinterpret_cast<long long*>(out), static_cast<cudaStream_t>(stream));
 }
+int b200xf_assemble_padded(const int64_t* flat_tokens, const int64_t* offsets, int first_row, int rows, int length, int64_t* out,
+                           int* too_long, void* stream) {
+  if (!flat_tokens || !offsets || !out || !too_long) return set_error("null argument");
+  return assemble_padded(reinterpret_cast<const long long*>(flat_tokens), reinterpret_cast<const long long*>(offsets), first_row, rows,
+                         length, reinterpret_cast<long long*>(out), too_long, static_cast<cudaStream_t>(stream));
+}
 int b200xf_synchronize(b200xf_ctx* ctx) {
   if (!ctx) return set_error("null ctx");
   B200XF_CUDA(cudaStreamSynchronize(ctx->c.stream));

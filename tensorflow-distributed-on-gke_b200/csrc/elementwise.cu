@@ -874,6 +874,35 @@ argmax_rows_kernel(const float* __restrict__ x, int ld, int cols, long long* __r
 }
 }  // namespace
 
+namespace {
+// Ragged -> dense: the `.to_tensor()` at the end of the reference's tokenisation (english_portugese_dataset.py:36-39)
+// pads every sentence of a batch with 0 (= PAD) to a common length.  flat holds the batch's sentences back to back,
+// offsets[r] .. offsets[r+1] delimit sentence r; one warp per output row, 16-byte stores when the row pitch allows.
+__global__ void __launch_bounds__(256)
+assemble_padded_kernel(const long long* __restrict__ flat, const long long* __restrict__ offsets, int first_row, int rows,
+                       int L, long long* __restrict__ out, int* __restrict__ too_long) {
+  pdl_wait();
+  pdl_trigger();
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  const long long b0 = offsets[first_row + warp], b1 = offsets[first_row + warp + 1];
+  const long long len = b1 - b0;
+  if (len > L && lane == 0) atomicMax(too_long, int(len));  // reported to the host: a sentence does not fit the row
+  long long* o = out + size_t(warp) * L;
+  for (int j = lane; j < L; j += 32) o[j] = (j < len) ? flat[b0 + j] : 0ll;
+}
+}  // namespace
+
+int assemble_padded(const long long* flat, const long long* offsets, int first_row, int rows, int L, long long* out,
+                    int* too_long_dev, cudaStream_t stream) {
+  if (rows <= 0 || L <= 0) return set_error("assemble_padded: empty batch (rows=%d L=%d)", rows, L);
+  if (first_row < 0) return set_error("assemble_padded: negative first row");
+  B200XF_CUDA(launch_k(assemble_padded_kernel, (rows * 32 + 255) / 256, 256, 0, stream, flat, offsets, first_row, rows, L, out, too_long_dev));
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
 int argmax_rows(const float* x, int ld, int rows, int cols, long long* out, cudaStream_t stream) {
   if (rows <= 0 || cols <= 0) return set_error("argmax: empty problem");
   B200XF_CUDA(launch_k(argmax_rows_kernel, rows, 256, 0, stream, x, ld, cols, out));

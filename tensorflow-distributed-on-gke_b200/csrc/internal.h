@@ -181,6 +181,10 @@ int colsum_parts(int rows, int cols);
 int colsum_partial(const bf16* x, int ld, int rows, int cols, float* partials, cudaStream_t stream);
 int cast_f32_to_bf16(const float* in, bf16* out, size_t n, cudaStream_t stream);
 int argmax_rows(const float* x, int ld, int rows, int cols, long long* out, cudaStream_t stream);  // first maximum wins
+// out[r][j] = j < len(first_row + r) ? flat[offsets[first_row + r] + j] : 0 for r < rows, j < L (english_portugese_dataset.py:36-39);
+// *too_long_dev (caller-zeroed) receives the longest length that did not fit L
+int assemble_padded(const long long* flat, const long long* offsets, int first_row, int rows, int L, long long* out,
+                    int* too_long_dev, cudaStream_t stream);
 int cast_bf16_to_f32_2d(const bf16* in, int ldi, float* out, int ldo, int rows, int cols, cudaStream_t stream);
 
 }  // namespace b200xf
