@@ -14,19 +14,29 @@ hp = dict(layers_count=cfg["layers_count"], embedding_size=cfg["embedding_size"]
           feed_forward_hidden_size=cfg["feed_forward_hidden_size"], input_vocabulary_size=cfg["input_vocabulary_size"],
           target_vocabulary_size=cfg["target_vocabulary_size"], maximum_input_length=max(1000, S), maximum_target_length=max(1000, T + 1),
           droput_rate=0.0)
+import os
+world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))
+torch.cuda.set_device(local)
+if world > 1:  # torchrun: profile rank 0 of a data-parallel job
+    import torch.distributed as dist
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 model = b200xf.Transformer(**hp, max_tokens=B * max(S, T + 1), seed=0)
 model.trainable_variables
+b200xf.B200Strategy(rank, world).attach(model)
 model.iterations = 1
-dev = torch.device("cuda:0")
+dev = torch.device("cuda", local)
 inp, tgt = b200xf.synthetic_batch(B, S, T + 1, hp["input_vocabulary_size"], hp["target_vocabulary_size"], seed=1, ragged=False)
 inp, tgt = torch.from_numpy(inp).to(dev), torch.from_numpy(tgt).to(dev)
 for _ in range(8):
-    model.train_step_device(inp, tgt)
+    model.train_step_device(inp, tgt, workers_count=world)
 torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     for _ in range(3):
-        model.train_step_device(inp, tgt)
+        model.train_step_device(inp, tgt, workers_count=world)
     torch.cuda.synchronize()
+if rank != 0:
+    model.close(); sys.exit(0)
 evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
 evs.sort(key=lambda e: e.time_range.start)
 if not evs:
