@@ -8,6 +8,9 @@ from b200xf import kernels as K
 
 
 def timeit(fn, reps=20):
+    if "--once" in sys.argv:  # for `ncu`: every kernel twice (cold, warm), no graph, no timing
+        fn(); fn(); torch.cuda.synchronize()
+        return float("nan")
     side = torch.cuda.Stream()
     g = torch.cuda.CUDAGraph()
     with torch.cuda.stream(side):
