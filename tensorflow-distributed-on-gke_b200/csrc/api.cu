@@ -121,6 +121,7 @@ int b200xf_synchronize(b200xf_ctx* ctx) {
   if (!ctx) return set_error("null ctx");
   B200XF_CUDA(cudaStreamSynchronize(ctx->c.stream));
   B200XF_CUDA(cudaStreamSynchronize(ctx->c.comm_stream));
+  B200XF_CUDA(cudaStreamSynchronize(ctx->c.upd_stream));
   B200XF_CUDA(cudaStreamSynchronize(ctx->c.side_stream));
   B200XF_CUDA(cudaStreamSynchronize(ctx->c.user_stream));
   return 0;

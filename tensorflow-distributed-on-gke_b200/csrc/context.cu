@@ -340,6 +340,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   adam.warmup_pow_m15 = float(pow(double(hp.warmup_steps), -1.5));
   B200XF_CUDA(cudaMallocHost(&host_out, 64));
   B200XF_CUDA(cudaStreamCreateWithFlags(&comm_stream, cudaStreamNonBlocking));
+  B200XF_CUDA(cudaStreamCreateWithFlags(&upd_stream, cudaStreamNonBlocking));
   B200XF_CUDA(cudaStreamCreateWithFlags(&side_stream, cudaStreamNonBlocking));
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
@@ -348,11 +349,16 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   if (const char* e = getenv("B200XF_GRAPH")) use_graph = atoi(e) != 0;
   if (const char* e = getenv("B200XF_SHARDED_UPDATE")) sharded_update = atoi(e) != 0;
   if (const char* e = getenv("B200XF_BUCKET_JOIN")) bucket_join = atoi(e) != 0;
+  if (const char* e = getenv("B200XF_PIPELINED_UPDATE")) pipelined_update = atoi(e);  // 0 off, 1 every bucket, 2 the last two bucket closes
   if (const char* e = getenv("B200XF_COMM_SMS")) comm_sms = std::max(0, atoi(e));
   if (const char* e = getenv("B200XF_WEIGHT_PREFETCH")) weights_static = atoi(e);  // bit mask, see context.h
   if (const char* e = getenv("B200XF_BUCKET_MB")) { bucket_bytes = size_t(std::max(1, atoi(e))) << 20; bucket_bytes_set = true; }
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_ready, cudaEventDisableTiming));
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_done, cudaEventDisableTiming));
+  B200XF_CUDA(cudaEventCreateWithFlags(&ev_rs, cudaEventDisableTiming));
+  B200XF_CUDA(cudaEventCreateWithFlags(&ev_adam[0], cudaEventDisableTiming));
+  B200XF_CUDA(cudaEventCreateWithFlags(&ev_adam[1], cudaEventDisableTiming));
+  B200XF_CUDA(cudaEventCreateWithFlags(&ev_ag, cudaEventDisableTiming));
   return 0;
 }
 
@@ -369,6 +375,8 @@ Context::~Context() {
   cudaFree(params); cudaFree(grads); cudaFree(adam_m); cudaFree(adam_v); cudaFree(shadow); cudaFree(arena);
   if (host_out) cudaFreeHost(host_out);
   if (comm_stream) cudaStreamDestroy(comm_stream);
+  if (upd_stream) cudaStreamDestroy(upd_stream);
+  for (cudaEvent_t e : {ev_rs, ev_adam[0], ev_adam[1], ev_ag}) if (e) cudaEventDestroy(e);
   if (side_stream) { cudaStreamSynchronize(side_stream); cudaStreamDestroy(side_stream); }
   if (ev_fork) cudaEventDestroy(ev_fork);
   if (ev_join) cudaEventDestroy(ev_join);
@@ -422,6 +430,7 @@ int Context::comm_destroy() {
   if (!comm) return 0;
   NcclApi* api = nccl_api();
   cudaStreamSynchronize(comm_stream);
+  if (upd_stream) cudaStreamSynchronize(upd_stream);
   if (api) api->CommDestroy(static_cast<ncclComm_t>(comm));
   comm = nullptr; world = 1; rank = 0;
   return 0;
@@ -819,16 +828,49 @@ int Context::section_done() {
     // weights and refresh the bf16 operand copy / clear the gradients of the whole bucket in one pass
     const size_t sh = n / world, off = bucket_begin + size_t(rank) * sh;
     ncclComm_t c = static_cast<ncclComm_t>(comm);
-    B200XF_NCCL(api->ReduceScatter(grads + bucket_begin, grads + off, sh, ncclFloat32, ncclSum, c, comm_stream));
-    B200XF_TRY(adam_step(params + off, grads + off, adam_m + off, adam_v + off, nullptr, sh, iterations_dev, adam, 0, comm_stream));
-    B200XF_NCCL(api->AllGather(params + off, params + bucket_begin, sh, ncclFloat32, c, comm_stream));
-    B200XF_TRY(refresh_shadow_zero_grad(params + bucket_begin, shadow + bucket_begin, grads + bucket_begin, n, comm_stream));
+    if (pipelined_update == 1 || (pipelined_update == 2 && idx + 2 >= sections.size())) {
+      // Collectives stay on the communicator's stream, Adam and the refresh pass go to a second one, and a bucket's
+      // all-gather is issued only after the NEXT bucket's reduce-scatter:  RS(k) | RS(k+1) + Adam(k) | AG(k) + Adam(k+1) |
+      // AG(k+1) + refresh(k) | refresh(k+1).  What is left when backward ends is two buckets' collectives back to back
+      // instead of two full reduce-scatter -> Adam -> all-gather -> refresh chains.
+      B200XF_NCCL(api->ReduceScatter(grads + bucket_begin, grads + off, sh, ncclFloat32, ncclSum, c, comm_stream));
+      B200XF_CUDA(cudaEventRecord(ev_rs, comm_stream));
+      B200XF_CUDA(cudaStreamWaitEvent(upd_stream, ev_rs, 0));
+      B200XF_TRY(adam_step(params + off, grads + off, adam_m + off, adam_v + off, nullptr, sh, iterations_dev, adam, 0, upd_stream));
+      B200XF_CUDA(cudaEventRecord(ev_adam[adam_slot], upd_stream));  // this bucket's Adam (two events, alternating per bucket)
+      if (pending_gather.valid) B200XF_TRY(flush_pending_gather());  // the PREVIOUS bucket's gather, behind this bucket's reduce-scatter
+      pending_gather = PendingGather{true, bucket_begin, off, sh, n, adam_slot};
+      adam_slot ^= 1;
+      upd_dirty = true;
+    } else {
+      B200XF_NCCL(api->ReduceScatter(grads + bucket_begin, grads + off, sh, ncclFloat32, ncclSum, c, comm_stream));
+      B200XF_TRY(adam_step(params + off, grads + off, adam_m + off, adam_v + off, nullptr, sh, iterations_dev, adam, 0, comm_stream));
+      B200XF_NCCL(api->AllGather(params + off, params + bucket_begin, sh, ncclFloat32, c, comm_stream));
+      B200XF_TRY(refresh_shadow_zero_grad(params + bucket_begin, shadow + bucket_begin, grads + bucket_begin, n, comm_stream));
+    }
   } else {
     if (comm) B200XF_TRY(allreduce(grads + bucket_begin, n, comm_stream));
     B200XF_TRY(adam_step(params + bucket_begin, grads + bucket_begin, adam_m + bucket_begin, adam_v + bucket_begin,
                          shadow + bucket_begin, n, iterations_dev, adam, 1, comm_stream));
   }
+  if (last && pending_gather.valid) B200XF_TRY(flush_pending_gather());
+  // (a bucket that did not take the pipelined path while a gather is pending cannot occur: the pipelined buckets are
+  // either all of them or the trailing ones)
   bucket_begin = end;
+  return 0;
+}
+
+// The all-gather of the bucket whose Adam was queued last (after that Adam), then its bf16 refresh / gradient clear.
+int Context::flush_pending_gather() {
+  const PendingGather g = pending_gather;
+  pending_gather.valid = false;
+  NcclApi* api = nccl_api();
+  B200XF_CUDA(cudaStreamWaitEvent(comm_stream, ev_adam[g.slot], 0));
+  B200XF_NCCL(api->AllGather(params + g.off, params + g.begin, g.sh, ncclFloat32, static_cast<ncclComm_t>(comm), comm_stream));
+  B200XF_CUDA(cudaEventRecord(ev_ag, comm_stream));
+  B200XF_CUDA(cudaStreamWaitEvent(upd_stream, ev_ag, 0));
+  B200XF_TRY(refresh_shadow_zero_grad(params + g.begin, shadow + g.begin, grads + g.begin, g.n, upd_stream));
+  upd_dirty = true;
   return 0;
 }
 
@@ -921,6 +963,7 @@ int Context::step_body(const long long* inp, const long long* target, int B, int
   if (mode >= 1) {
     overlap_update = (mode == 2) && (comm != nullptr || overlap_single);
     bucket_begin = 0;
+    pending_gather.valid = false;
     B200XF_TRY(backward(inp, tok_tgt_in, B, S, T));
   }
   B200XF_TRY(phase_mark(3));
@@ -933,6 +976,11 @@ int Context::step_body(const long long* inp, const long long* target, int B, int
       B200XF_TRY(allreduce(metrics + 3, 3, comm_stream));
     }
     if (overlap_update) {
+      if (upd_dirty) {  // the second update stream rejoins too
+        B200XF_CUDA(cudaEventRecord(ev_ag, upd_stream));
+        B200XF_CUDA(cudaStreamWaitEvent(stream, ev_ag, 0));
+        upd_dirty = false;
+      }
       B200XF_CUDA(cudaEventRecord(ev_done, comm_stream));
       B200XF_CUDA(cudaStreamWaitEvent(stream, ev_done, 0));  // every bucket's update (and the metrics) done before what follows
     } else {
