@@ -115,7 +115,7 @@ int b200xf_forward_backward_device(b200xf_ctx* ctx, const int64_t* inp, const in
 int b200xf_synchronize(b200xf_ctx* ctx);
 
 /* Dropout(rate) (transformer_model.py:190-191,223-225,268,299; applied at :196,202,232,238,244,276,308) is inverted
- * dropout from a counter-based generator keyed by (seed, site, optimizer.iterations, element index): nothing is stored,
+ * dropout from a counter-based generator keyed by (seed, replica rank, site, optimizer.iterations, element index): nothing is stored,
  * the backward pass recomputes the same mask.  TensorFlow's random stream cannot be matched, so the checker reads the
  * mask itself: b200xf_dropout_mask writes, for dropout site `site` at the CURRENT iterations value, a DEVICE fp32
  * [rows, cols] array holding 1/(1-rate) where the element is kept and 0 where it is dropped.  Sites: 0 / 1 encoder /
@@ -133,8 +133,15 @@ int b200xf_comm_destroy(b200xf_ctx* ctx);
 /* With more than one rank a train step reduce-scatters each gradient bucket, applies Adam to the local 1/world shard and
  * all-gathers the updated weights (same wire bytes as an all-reduce, 1/world of the optimizer traffic): every rank ends
  * with identical fp32 weights, but adam_m / adam_v are then only maintained for the local shard of each bucket.
- * B200XF_SHARDED_UPDATE=0 selects all-reduce + replicated Adam.
- * All-reduce (SUM, fp32, in place) of `count` floats at DEVICE pointer on the context's comm stream. */
+ * B200XF_SHARDED_UPDATE=0 selects all-reduce + replicated Adam (the reference's mirrored optimizer slots, cluster/cluster.py:66).
+ * b200xf_gather_optimizer_state is the collective (every rank calls it) that completes adam_m / adam_v on all ranks by
+ * all-gathering the shards — call it before reading the slots for a checkpoint or before detaching the communicator;
+ * b200xf_optimizer_state_complete returns 1 when the slots are current everywhere (always with one rank), else 0.
+ * Bucket boundaries follow from the layout and B200XF_BUCKET_MB, so keep both unchanged for the life of a training run.
+ * Each replica draws its own dropout masks: the rank is part of the mask key (see b200xf_set_dropout_seed). */
+int b200xf_gather_optimizer_state(b200xf_ctx* ctx);
+int b200xf_optimizer_state_complete(b200xf_ctx* ctx);
+/* All-reduce (SUM, fp32, in place) of `count` floats at DEVICE pointer on the context's comm stream. */
 int b200xf_allreduce_bucket(b200xf_ctx* ctx, float* device_ptr, int64_t count);
 
 /* ---- per-kernel entry points (unit tests, ncu).  All pointers are DEVICE pointers, `stream` a cudaStream_t. */

@@ -1,15 +1,8 @@
 #!/bin/bash
-# Runs the GPU test groups in separate processes (a sticky CUDA fault in one group must not hide the others).
-# Usage (on the GPU box): bash scripts/gpu_check.sh [group ...]
-cd "$(dirname "$0")/.."
+# GPU-box check of the whole tree: GPU tests, smoke(), one bench line.  Logs land in gpurun_out/.
 mkdir -p gpurun_out
-groups=("$@")
-[ ${#groups[@]} -eq 0 ] && groups=(gemm attention layernorm embedding positional vocab_ce adam train_step)
-for g in "${groups[@]}"; do
-  case $g in
-    train_step) sel="tests/test_train_step_gpu.py" ;;
-    *) sel="tests/test_kernels_gpu.py -k $g" ;;
-  esac
-  echo "=== $g"
-  timeout 600 python -m pytest $sel -q -m gpu --timeout 120 --timeout-method=thread $XFLAG -q 2>&1 | grep -v "Warning\|warnings.html\|^$\|Triggered\|Consider" | tail -${TAILN:-40} | tee gpurun_out/test_$g.log
-done
+nvidia-smi -L > gpurun_out/gpus.txt
+timeout 1300 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+tail -15 gpurun_out/pytest_gpu.log
+timeout 200 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; tail -3 gpurun_out/smoke.log
+timeout 600 python bench.py --steps ${BENCH_STEPS:-100} --warmup 5 > gpurun_out/bench.log 2> gpurun_out/bench.err; tail -c 6000 gpurun_out/bench.log; tail -5 gpurun_out/bench.err

@@ -64,6 +64,8 @@ SIGNATURES = {
     "b200xf_comm_unique_id": (_I, [_P]),
     "b200xf_comm_init": (_I, [_P, _P, _I, _I]),
     "b200xf_comm_destroy": (_I, [_P]),
+    "b200xf_gather_optimizer_state": (_I, [_P]),
+    "b200xf_optimizer_state_complete": (_I, [_P]),
     "b200xf_allreduce_bucket": (_I, [_P, _P, _L]),
     "b200xf_gemm_bf16": (_I, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _I, _I, _I, _P, _I, _P, _I, _I, _F, _I, _I, _P]),
     "b200xf_assemble_padded": (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),

@@ -49,12 +49,14 @@ def padded_length(offsets, length_multiple=1, maximum_length=None):
 
 
 def replica_rows(global_rows, rank, world):
-    """Contiguous slice of a global batch that replica `rank` keeps (same rule as B200Strategy.experimental_distribute_dataset:
-    every replica gets floor(rows / world) rows, a remainder is dropped)."""
+    """Contiguous slice (first row, row count) of a global batch that replica `rank` keeps — the rule of
+    B200Strategy.experimental_distribute_dataset.  No row is dropped: when the global batch does not divide evenly (the
+    last batch of an epoch, __main__.py:95-99) the first `rows % world` replicas take one row more, as the per-replica
+    re-batching of tf.distribute does (sizes differ by at most one)."""
     if not 0 <= rank < world:
         raise ValueError(f"rank {rank} outside a world of {world}")
-    n = global_rows // world
-    return rank * n, n
+    n, rem = divmod(global_rows, world)
+    return rank * n + min(rank, rem), n + (1 if rank < rem else 0)
 
 
 def pad_to_longest(sentences, length=None):

@@ -133,6 +133,11 @@ int b200xf_comm_init(b200xf_ctx* ctx, const void* id, int rank, int world) {
   return ctx->c.comm_init(id, rank, world);
 }
 int b200xf_comm_destroy(b200xf_ctx* ctx) { return ctx ? ctx->c.comm_destroy() : set_error("null ctx"); }
+int b200xf_gather_optimizer_state(b200xf_ctx* ctx) {
+  if (!ctx) return set_error("null ctx");
+  B200XF_SCOPED(ctx, ctx->c.gather_optimizer_state());
+}
+int b200xf_optimizer_state_complete(b200xf_ctx* ctx) { return (ctx && ctx->c.opt_state_complete) ? 1 : 0; }
 int b200xf_allreduce_bucket(b200xf_ctx* ctx, float* ptr, int64_t count) {
   if (!ctx || !ptr) return set_error("null argument");
   B200XF_TRY(ctx->c.enter());

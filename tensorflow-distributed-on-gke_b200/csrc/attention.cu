@@ -466,16 +466,7 @@ KernelArgs pack(const AttnArgs& a) {
 
 template <typename Kern>
 int launch_attn(Kern kern, size_t smem, dim3 grid, const KernelArgs& p, cudaStream_t stream) {
-  if (smem > 48 * 1024) {
-    static std::mutex mu;
-    static std::set<const void*> configured;
-    std::lock_guard<std::mutex> lock(mu);
-    if (!configured.count(reinterpret_cast<const void*>(kern))) {
-      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-      if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(attention): %s", cudaGetErrorString(e));
-      configured.insert(reinterpret_cast<const void*>(kern));
-    }
-  }
+  if (smem > 48 * 1024) B200XF_TRY(ensure_dynamic_smem(kern, int(smem)));
   B200XF_CUDA(launch_k(kern, grid, kWarps * 32, smem, stream, p));
   count_launch();
   return 0;

@@ -760,10 +760,11 @@ attn_bwd_dq_out_kernel(const float* __restrict__ dq_acc, bf16* __restrict__ dq, 
 
 // Measured on B200 (scripts/kernel_bench.py long / big): this forward is on par with the mma.sync kernel (63 vs 67 us causal,
 // 91 vs 89 us non-causal at B8 H8 S1024; 30 vs 26 us at S256) because one CTA serialises S -> softmax -> PV, so it is opt-in
-// (B200XF_ATTENTION_TC_FWD_MULTI=1, read at every call) until it ping-pongs two query tiles per CTA.
+// (B200XF_ATTENTION_TC_FWD_MULTI=1, read once) until it ping-pongs two query tiles per CTA.
 bool attention_tc_fwd_multi_supported(const AttnArgs& a) {
-  const char* e = getenv("B200XF_ATTENTION_TC_FWD_MULTI");
-  return e && atoi(e) != 0 && a.dk == kD && a.Sq > 0 && a.Sk > 0;
+  static int enabled = -1;  // read once
+  if (enabled < 0) { const char* e = getenv("B200XF_ATTENTION_TC_FWD_MULTI"); enabled = (e && atoi(e) != 0) ? 1 : 0; }
+  return enabled && a.dk == kD && a.Sq > 0 && a.Sk > 0;
 }
 
 int attention_fwd_tc_multi(const AttnArgs& a, cudaStream_t stream) {
@@ -776,10 +777,7 @@ int attention_fwd_tc_multi(const AttnArgs& a, cudaStream_t stream) {
   p.key_tokens = a.key_tokens; p.o = a.o; p.ldo = a.ldo; p.lse = a.lse;
   p.H = a.H; p.Sq = a.Sq; p.Sk = a.Sk; p.causal = a.causal;
   p.scale = 1.0f / sqrtf(float(a.dk)); p.scale_log2 = p.scale * kLog2e;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] { attr_err = cudaFuncSetAttribute(attn_fwd_tc_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemFwdMulti); });
-  if (attr_err != cudaSuccess) return set_error("cudaFuncSetAttribute(attn_fwd_tc_multi): %s", cudaGetErrorString(attr_err));
+  B200XF_TRY(ensure_dynamic_smem(attn_fwd_tc_multi_kernel, kSmemFwdMulti));
   B200XF_CUDA(launch_k(attn_fwd_tc_multi_kernel, dim3((a.Sq + kT - 1) / kT, a.H, a.B), kThreadsMulti, kSmemFwdMulti, stream, tq, tk, tv, p));
   count_launch();
   return 0;
@@ -807,10 +805,7 @@ int attention_bwd_tc_multi(const AttnArgs& a, cudaStream_t stream) {
   p.dk_out = a.dk_out; p.dv_out = a.dv_out; p.lddk = a.lddk; p.lddv = a.lddv;
   p.H = a.H; p.Sq = a.Sq; p.Sk = a.Sk; p.causal = a.causal;
   p.scale = 1.0f / sqrtf(float(a.dk)); p.scale_log2 = p.scale * kLog2e;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] { attr_err = cudaFuncSetAttribute(attn_bwd_tc_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBwdMulti); });
-  if (attr_err != cudaSuccess) return set_error("cudaFuncSetAttribute(attn_bwd_tc_multi): %s", cudaGetErrorString(attr_err));
+  B200XF_TRY(ensure_dynamic_smem(attn_bwd_tc_multi_kernel, kSmemBwdMulti));
   B200XF_CUDA(launch_k(attn_bwd_tc_multi_kernel, dim3((a.Sk + kT - 1) / kT, a.H, a.B), kThreadsMulti, kSmemBwdMulti, stream, tq, tk, tv, tdo, tdq, p));
   const size_t total = size_t(rows) * cols;
   B200XF_CUDA(launch_k(attn_bwd_dq_out_kernel, int(std::min<size_t>((total / 4 + 255) / 256, 4096)), 256, 0, stream,
@@ -836,10 +831,7 @@ int attention_fwd_tc(const AttnArgs& a, cudaStream_t stream) {
   p.H = a.H; p.Sq = a.Sq; p.Sk = a.Sk; p.causal = a.causal;
   p.scale = 1.0f / sqrtf(float(a.dk)); p.scale_log2 = p.scale * kLog2e;
   p.early = a.early;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] { attr_err = cudaFuncSetAttribute(attn_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemFwd); });
-  if (attr_err != cudaSuccess) return set_error("cudaFuncSetAttribute(attn_fwd_tc): %s", cudaGetErrorString(attr_err));
+  B200XF_TRY(ensure_dynamic_smem(attn_fwd_tc_kernel, kSmemFwd));
   B200XF_CUDA(launch_k(attn_fwd_tc_kernel, dim3(a.H, a.B), kThreads, kSmemFwd, stream, tq, tk, tv, p));
   count_launch();
   return 0;
@@ -858,10 +850,7 @@ int attention_bwd_tc(const AttnArgs& a, cudaStream_t stream) {
   p.H = a.H; p.Sq = a.Sq; p.Sk = a.Sk; p.causal = a.causal;
   p.scale = 1.0f / sqrtf(float(a.dk)); p.scale_log2 = p.scale * kLog2e;
   p.early = a.early;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] { attr_err = cudaFuncSetAttribute(attn_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBwd); });
-  if (attr_err != cudaSuccess) return set_error("cudaFuncSetAttribute(attn_bwd_tc): %s", cudaGetErrorString(attr_err));
+  B200XF_TRY(ensure_dynamic_smem(attn_bwd_tc_kernel, kSmemBwd));
   B200XF_CUDA(launch_k(attn_bwd_tc_kernel, dim3(a.H, a.B), kThreads2, kSmemBwd, stream, tq, tk, tv, tdo, p));
   count_launch();
   return 0;

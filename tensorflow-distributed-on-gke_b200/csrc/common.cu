@@ -3,6 +3,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 
 #include "internal.h"
 
@@ -48,6 +49,29 @@ int stream_priority(cudaStream_t stream) {
   if (cudaStreamGetPriority(stream, &prio) != cudaSuccess) { (void)cudaGetLastError(); prio = 0; }
   if (used < 8) { keys[used] = stream; vals[used] = prio; ++used; }
   return prio;
+}
+
+int ensure_dynamic_smem(const void* kernel, int bytes) {
+  struct Entry { const void* kernel; unsigned long long devices; int bytes; };
+  static Entry table[256];
+  static int used = 0;
+  static std::mutex mu;
+  int dev = 0;
+  B200XF_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return set_error("device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  Entry* e = nullptr;
+  for (int i = 0; i < used; ++i) if (table[i].kernel == kernel) { e = &table[i]; break; }
+  if (!e) {
+    if (used == 256) return set_error("kernel attribute table full");
+    e = &table[used++]; e->kernel = kernel; e->devices = 0; e->bytes = 0;
+  }
+  if (((e->devices >> dev) & 1ull) && e->bytes >= bytes) return 0;
+  if (bytes > e->bytes) { e->bytes = bytes; e->devices = 0; }
+  const cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, e->bytes);
+  if (err != cudaSuccess) return set_error("cudaFuncSetAttribute(MaxDynamicSharedMemorySize=%d): %s", e->bytes, cudaGetErrorString(err));
+  e->devices |= 1ull << dev;
+  return 0;
 }
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }

@@ -347,7 +347,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   if (const char* e = getenv("B200XF_SIDE_WGRAD")) side_on = atoi(e) != 0;
   if (const char* e = getenv("B200XF_PHASE_TIMING")) phase_timing = atoi(e) != 0;
   if (const char* e = getenv("B200XF_GRAPH")) use_graph = atoi(e) != 0;
-  if (const char* e = getenv("B200XF_SHARDED_UPDATE")) sharded_update = atoi(e) != 0;
+  if (const char* e = getenv("B200XF_SHARDED_UPDATE")) sharded_update = std::max(0, std::min(2, atoi(e)));
   if (const char* e = getenv("B200XF_BUCKET_JOIN")) bucket_join = atoi(e) != 0;
   if (const char* e = getenv("B200XF_PIPELINED_UPDATE")) pipelined_update = atoi(e);  // 0 off, 1 every bucket, 2 the last two bucket closes
   if (const char* e = getenv("B200XF_COMM_SMS")) comm_sms = std::max(0, atoi(e));
@@ -424,6 +424,7 @@ int Context::comm_init(const void* id128, int rank_, int world_) {
   ncclComm_t c;
   B200XF_NCCL(api->CommInitRank(&c, world_, id, rank_));
   comm = c; rank = rank_; world = world_;
+  drop_graphs();  // steps captured without (or with another) communicator must not be replayed
   return 0;
 }
 int Context::comm_destroy() {
@@ -431,6 +432,7 @@ int Context::comm_destroy() {
   NcclApi* api = nccl_api();
   cudaStreamSynchronize(comm_stream);
   if (upd_stream) cudaStreamSynchronize(upd_stream);
+  drop_graphs();  // captured steps hold collectives of the communicator that goes away
   if (api) api->CommDestroy(static_cast<ncclComm_t>(comm));
   comm = nullptr; world = 1; rank = 0;
   return 0;
@@ -450,6 +452,9 @@ DropArgs Context::site_drop(int site) const {
   if (!dropout_on) return d;
   d.step = iterations_dev;
   d.key = (dropout_seed * 0x9E3779B97F4A7C15ull) ^ (static_cast<unsigned long long>(site + 1) * 0xC2B2AE3D27D4EB4Full);
+  // Each replica draws its own masks, as the workers of MultiWorkerMirroredStrategy do (every worker has its own RNG):
+  // the replica's rank is part of the key.  A mask is reproduced by the same (seed, rank, site, iterations).
+  d.key ^= static_cast<unsigned long long>(rank) * 0xD6E8FEB86659FD93ull;
   const double t = double(hp.droput_rate) * 4294967296.0;
   d.thresh = t >= 4294967295.0 ? 4294967295u : static_cast<unsigned>(t);
   d.scale = 1.0f / (1.0f - hp.droput_rate);
@@ -802,7 +807,7 @@ int Context::section_done() {
   // own bucket (several small optimizer launches disturb the backward pass less than a few large ones: 4.10 vs 4.13 ms)
   // (smaller buckets towards the end of backward, to shorten what is left queued behind the collectives when backward
   // ends, measured slower on 2 GPUs: 4.63 ms against 4.46 -- more collective launches, each disturbing the GEMMs)
-  const size_t want = bucket_bytes_set ? bucket_bytes : (comm ? bucket_bytes : (size_t(8) << 20));
+  const size_t want = bucket_want_bytes();
   if (!last && (end - bucket_begin) * sizeof(float) < want) return 0;
   // The bucket's gradients come from the compute stream (LayerNorm partials, embedding rows) and from the side stream
   // (weight gradients, bias partials).  Default: the compute stream waits for the side stream here and sums the partials
@@ -822,7 +827,7 @@ int Context::section_done() {
   B200XF_TRY(flush_reductions(comm_stream));
   const size_t n = end - bucket_begin;
   NcclApi* api = comm ? nccl_api() : nullptr;
-  if (comm && sharded_update && world > 1 && api->ReduceScatter && api->AllGather && n % (size_t(world) * 64) == 0) {
+  if (sharded_active() && api->ReduceScatter && api->AllGather && n % (size_t(world) * 64) == 0) {
     // all-reduce = reduce-scatter + all-gather: put the Adam update between the two halves, on this rank's 1/world
     // shard only (same bytes on the wire, 1/world of the optimizer's HBM traffic), then gather the updated fp32
     // weights and refresh the bf16 operand copy / clear the gradients of the whole bucket in one pass
@@ -857,6 +862,36 @@ int Context::section_done() {
   // (a bucket that did not take the pipelined path while a gather is pending cannot occur: the pipelined buckets are
   // either all of them or the trailing ones)
   bucket_begin = end;
+  return 0;
+}
+
+// The optimizer buckets of a train step: consecutive layout sections grouped until a bucket holds bucket_want_bytes().
+std::vector<std::pair<size_t, size_t>> Context::bucket_ranges() const {
+  std::vector<std::pair<size_t, size_t>> out;
+  size_t begin = 0;
+  for (size_t i = 0; i < sections.size(); ++i) {
+    const size_t end = sections[i].second;
+    if (i + 1 == sections.size() || (end - begin) * sizeof(float) >= bucket_want_bytes()) { out.push_back({begin, end}); begin = end; }
+  }
+  return out;
+}
+
+int Context::gather_optimizer_state() {
+  if (opt_state_complete || !sharded_active() || world == 1) { opt_state_complete = true; return 0; }
+  NcclApi* api = nccl_api();
+  ncclComm_t c = static_cast<ncclComm_t>(comm);
+  B200XF_CUDA(cudaEventRecord(ev_ready, stream));
+  B200XF_CUDA(cudaStreamWaitEvent(comm_stream, ev_ready, 0));
+  for (const auto& b : bucket_ranges()) {
+    const size_t n = b.second - b.first;
+    if (n % (size_t(world) * 64)) continue;  // such a bucket took the replicated update: complete everywhere already
+    const size_t sh = n / world, off = b.first + size_t(rank) * sh;
+    B200XF_NCCL(api->AllGather(adam_m + off, adam_m + b.first, sh, ncclFloat32, c, comm_stream));
+    B200XF_NCCL(api->AllGather(adam_v + off, adam_v + b.first, sh, ncclFloat32, c, comm_stream));
+  }
+  B200XF_CUDA(cudaEventRecord(ev_done, comm_stream));
+  B200XF_CUDA(cudaStreamWaitEvent(stream, ev_done, 0));
+  opt_state_complete = true;
   return 0;
 }
 
@@ -939,6 +974,9 @@ int Context::step_device(const long long* inp, const long long* target, int B, i
     }
     StepGraph& cur = graphs[{B, S, T1, workers_count}];
     if (cur.exec) {
+      // The captured step starts from cleared gradients (each step's optimizer pass leaves them so) and therefore holds
+      // no memset; a forward_backward call in between leaves gradients behind, which are cleared here, outside the graph.
+      if (!grads_clean) B200XF_CUDA(cudaMemsetAsync(grads, 0, total_params * sizeof(float), stream));
       B200XF_CUDA(cudaGraphLaunch(cur.exec, stream));
       if (cur.counted) count_launch(cur.launches); else cur.counted = true;  // the capture itself already counted them once
       grads_clean = true;
@@ -949,6 +987,7 @@ int Context::step_device(const long long* inp, const long long* target, int B, i
     B200XF_TRY(step_body(inp, target, B, S, T1, workers_count, mode));
   }
   if (out6) B200XF_CUDA(cudaMemcpyAsync(out6, metrics, 6 * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  if (mode == 2 && sharded_active() && world > 1) opt_state_complete = false;  // m / v now current on the local shards only
   return 0;
 }
 

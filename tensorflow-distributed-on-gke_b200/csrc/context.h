@@ -97,7 +97,16 @@ struct Context {
   size_t bucket_bytes = size_t(32) << 20, bucket_begin = 0, next_section = 0;
   // With several ranks each bucket is reduce-scattered, updated on the local 1/world shard and all-gathered (Adam m / v
   // are then only maintained for the local shard of every bucket).  B200XF_SHARDED_UPDATE=0 keeps the replicated update.
-  bool sharded_update = true;
+  // 2 = also with a one-rank communicator (exercises the sharded / pipelined chain on a single GPU; tests).
+  int sharded_update = 1;
+  bool sharded_active() const { return comm && sharded_update && (world > 1 || sharded_update == 2); }
+  // After a sharded step Adam's m / v are current only on this rank's shard of every bucket; gather_optimizer_state
+  // (a collective: every rank calls it) completes them everywhere.
+  bool opt_state_complete = true;
+  // With a communicator a bucket must amortise a collective's latency; alone, buckets of >= 8 MB.
+  size_t bucket_want_bytes() const { return bucket_bytes_set ? bucket_bytes : (comm ? bucket_bytes : (size_t(8) << 20)); }
+  std::vector<std::pair<size_t, size_t>> bucket_ranges() const;
+  int gather_optimizer_state();
   // the bf16 weight copy is only written by the optimizer, never by the kernel just before a forward / data-gradient
   // GEMM on the compute stream, so those GEMMs may fetch their first weight tiles ahead of the dependency wait
   // Bit mask of the loads issued ahead of the dependency wait (B200XF_WEIGHT_PREFETCH): 1 weight tiles in forward /

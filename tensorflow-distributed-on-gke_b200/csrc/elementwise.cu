@@ -4,7 +4,6 @@
 // All global accesses are 128-bit vectorised and coalesced; reductions use warp shuffles.
 #include <algorithm>
 #include <mutex>
-#include <set>
 
 #include <cub/device/device_radix_sort.cuh>
 
@@ -281,14 +280,7 @@ int layernorm_bwd_partial(const bf16* dy, const bf16* z, const float* mean, cons
   const int ch = (d + 255) / 256;
   const size_t smem = size_t(kLnWarps) * 3 * d * sizeof(float);
   auto launch = [&](auto kern) -> int {
-    if (smem > 48 * 1024) {
-      static std::mutex mu; static std::set<const void*> done;
-      std::lock_guard<std::mutex> lock(mu);
-      if (!done.count(reinterpret_cast<const void*>(kern))) {
-        B200XF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kLnWarps * 3 * 2048 * sizeof(float))));
-        done.insert(reinterpret_cast<const void*>(kern));
-      }
-    }
+    if (smem > 48 * 1024) B200XF_TRY(ensure_dynamic_smem(kern, int(kLnWarps * 3 * 2048 * sizeof(float))));
     B200XF_CUDA(launch_k(kern, grid, kLnWarps * 32, smem, stream, dy, z, mean, rstd, gamma, dz, rows, d, partials, dzm, drop));
     return 0;
   };

@@ -487,12 +487,7 @@ int get_tmap(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint3
 template <int BN, int A_MN, int B_MN, bool PAIR>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const GemmParams& p, int grid, cudaStream_t stream) {
   auto kern = gemm_kernel<BN, A_MN, B_MN, PAIR>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, PAIR>::kSmem);
-    if (e != cudaSuccess) return set_error("cudaFuncSetAttribute(gemm): %s", cudaGetErrorString(e));
-    attr_set = true;
-  }
+  B200XF_TRY(ensure_dynamic_smem(kern, Cfg<BN, PAIR>::kSmem));
   cudaError_t e = launch_k_cluster(kern, grid, kThreads, Cfg<BN, PAIR>::kSmem, stream, PAIR ? 2 : 1, ta, tb, td, p);
   if (e != cudaSuccess) return set_error("gemm launch: %s", cudaGetErrorString(e));
   count_launch();

@@ -20,6 +20,10 @@ void count_launch(int n = 1);
 long long launches_total();
 
 bool pdl_enabled();  // B200XF_PDL=0 switches programmatic dependent launch off
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE property of a kernel: raise it once per (kernel, device),
+// with the launching device current.  Fixed-size table, no heap use.
+int ensure_dynamic_smem(const void* kernel, int bytes);
+template <typename K> inline int ensure_dynamic_smem(K* kernel, int bytes) { return ensure_dynamic_smem(reinterpret_cast<const void*>(kernel), bytes); }
 int stream_priority(cudaStream_t stream);  // cached cudaStreamGetPriority
 
 // Launch with the programmatic-stream-serialization attribute (see ptx.cuh: pdl_wait / pdl_trigger).
@@ -83,8 +87,20 @@ struct GemmArgs {
   int b_static = 0;      // B (weights) is not written by the kernel launched just before: prefetch it ahead of the dependency wait
   int pair = 0;          // CTA pairs (cta_group::2, 256-row tiles): 0 auto, 1 force when M >= 256, -1 never
   DropArgs drop;         // inverted dropout on (acc + bias) before the residual add (transformer_model.py:196,202,232,238,244)
+  // Weight-gradient layout only (a_mn = b_mn = 1): also emit the column sums of B over the contraction dimension -- the bias
+  // gradient sum_tokens dY[token][n] of the Dense whose weight gradient this is -- as one partial row per K split:
+  // colsum_partials[z * N + n], z < GemmInfo::splits (summed later by reduce_partials).  B's tiles are already in shared memory.
+  float* colsum_partials = nullptr;
+  // LayerNorm fused into the epilogue (N = the normalised width, bf16 output, no accumulate): d receives
+  // z = epilogue(acc) (bias, dropout, residual add), ln_y receives (z - mean) * rstd * gamma + beta with the statistics taken
+  // over the bf16-rounded z, ln_mean / ln_rstd the per-row statistics.  The CTAs that hold one row block's N tiles form a
+  // thread-block cluster and exchange their per-row partial statistics through distributed shared memory.
+  const float* ln_gamma = nullptr; const float* ln_beta = nullptr;
+  void* ln_y = nullptr; int ln_ldy = 0; float* ln_mean = nullptr; float* ln_rstd = nullptr; float ln_eps = 1e-6f;
 };
-int gemm_bf16(const GemmArgs& a, cudaStream_t stream);
+struct GemmInfo { int splits = 1; int tiles_m = 0, tiles_n = 0; int bn = 0; int pair = 0; int fused_ln = 0; };
+bool gemm_ln_fusable(int M, int N);  // whether a GEMM of width N can carry the fused LayerNorm epilogue
+int gemm_bf16(const GemmArgs& a, cudaStream_t stream, GemmInfo* info = nullptr);
 void gemm_clear_tensor_map_cache();
 void gemm_set_pair_mode(int mode);  // CTA pairs: -1 heuristic (default), 0 never, 1 whenever M > 128 and the tile is >= 128 wide
 // Cached 2-D TMA descriptor (128B swizzle) of a row-major matrix: kind 0 = bf16 with a 64-column box, 1 = fp32 with a

@@ -138,10 +138,12 @@ class B200Strategy:
         batches and keeps its own contiguous slice of each."""
         rank, world = self.rank, self.world_size
 
+        from .batching import replica_rows
+
         def gen():
             for inp, tgt in dataset:
-                n = len(inp) // world
-                yield inp[rank * n:(rank + 1) * n], tgt[rank * n:(rank + 1) * n]
+                first, n = replica_rows(len(inp), rank, world)  # uneven batches: sizes differ by at most one, none dropped
+                yield inp[first:first + n], tgt[first:first + n]
         return gen()
 
 

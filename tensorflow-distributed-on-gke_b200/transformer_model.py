@@ -295,9 +295,18 @@ class Transformer:
             v.assign(arrays[v.name])
         self._sync_weights()
 
+    def gather_optimizer_state(self):
+        """Collective (every replica calls it): after sharded multi-replica steps each replica holds current Adam slots
+        only for its shard of every bucket; this all-gathers them so that every replica holds all of m and v."""
+        self._ensure_built()
+        check(_lib.load().b200xf_gather_optimizer_state(self._ctx))
+
     def get_slot_dict(self, kind):
         """Adam slots (`adam_m` / `adam_v`) or `grad`, as {name: ndarray}."""
         flat = self._flat(kind)
+        if kind in ("adam_m", "adam_v") and not _lib.load().b200xf_optimizer_state_complete(self._ctx):
+            raise _lib.B200XFError(f"{kind} is sharded across replicas after a multi-replica step: call "
+                                   "gather_optimizer_state() on every replica first")
         return OrderedDict((v.name, v._view(flat).detach().cpu().numpy().copy()) for v in self.variables)
 
     def create_masks(self, input, target):

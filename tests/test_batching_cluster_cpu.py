@@ -57,7 +57,7 @@ def test_replica_rows_match_the_strategy_split():
             shard = next(iter(b200xf.B200Strategy(rank, world).experimental_distribute_dataset([(dense, dense)])))
             assert np.array_equal(shard[0], dense[first:first + rows])
             covered += list(range(first, first + rows))
-        assert covered == list(range(len(sents) // world * world))  # contiguous, disjoint, remainder dropped
+        assert covered == list(range(len(sents)))  # contiguous, disjoint, every row kept (sizes differ by at most one)
     with pytest.raises(ValueError):
         b200xf.replica_rows(8, 2, 2)
 

@@ -51,56 +51,100 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _rank_main(rank, world, port, out_dir):
+# several 1 MB buckets (final layer, decoder layers, embeddings + K|V, encoder layers): the RS(k+1) / AG(k) interleave of the
+# pipelined sharded update and its alternating event slots run; 6 steps of one shape, so steps 3+ replay the captured graph
+HP2 = dict(layers_count=3, embedding_size=128, heads_count=2, feed_forward_hidden_size=512, input_vocabulary_size=5000,
+           target_vocabulary_size=5000, maximum_input_length=200, maximum_target_length=200, droput_rate=0.0)
+STEPS2, B2, S2, T2 = 6, 8, 48, 48
+
+
+def _rank_main(rank, world, port, out_dir, env):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    os.environ.update(env)
     import torch.distributed as dist
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
-    model = b200xf.Transformer(**HP, seed=2, device=f"cuda:{rank}")
+    model = b200xf.Transformer(**HP2, seed=2, device=f"cuda:{rank}")
     strategy = b200xf.B200Strategy(rank, world)
     with strategy.scope():
         model.trainable_variables
         strategy.attach(model)
     model.iterations = 500
     res = []
-    for step in range(3):
-        glob = b200xf.synthetic_batch(4 * world, 20, 18, 203, 157, seed=70 + step, ragged=True)
+    for step in range(STEPS2):
+        glob = b200xf.synthetic_batch(B2 * world, S2, T2 + 1, 5000, 5000, seed=70 + step, ragged=True)
         inp, tgt = next(iter(strategy.experimental_distribute_dataset([glob])))
         res.append(model.train_step_device(inp, tgt, world).cpu().numpy())
     w = model.get_weights_dict()
-    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), res=np.stack(res), **{k.replace("/", "|"): v for k, v in w.items()})
+    sharded = os.environ.get("B200XF_SHARDED_UPDATE", "1") != "0"
+    raised = False
+    try:
+        model.get_slot_dict("adam_m")
+    except b200xf.B200XFError:
+        raised = True
+    assert raised == sharded, "sharded Adam slots must not be readable before gather_optimizer_state()"
+    model.gather_optimizer_state()
+    m = model.get_slot_dict("adam_m"); v = model.get_slot_dict("adam_v")
+    # dropout: every replica draws its own masks (the rank is part of the key)
+    hp_drop = dict(HP2, droput_rate=0.1)
+    dm = b200xf.Transformer(**hp_drop, seed=2, device=f"cuda:{rank}")
+    dm.trainable_variables
+    strategy.attach(dm)
+    mask = dm.dropout_mask(2, 64).cpu().numpy()
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), res=np.stack(res), mask=mask,
+             **{"w|" + k.replace("/", "|"): a for k, a in w.items()}, **{"m|" + k.replace("/", "|"): a for k, a in m.items()},
+             **{"v|" + k.replace("/", "|"): a for k, a in v.items()})
     dist.barrier()
+    dm.close(); model.close()
     dist.destroy_process_group()
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-def test_two_ranks_match_oracle_and_each_other(tmp_path):
-    import torch.multiprocessing as mp
-    world = 2
-    mp.spawn(_rank_main, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
-    z = [np.load(tmp_path / f"rank{r}.npz") for r in range(world)]
-    names = [k for k in z[0].files if k != "res"]
-    for k in names:  # mirrored variables: every replica holds the same weights after the all-reduced update
-        assert _rel(z[1][k], z[0][k]) < 1e-6, k
-    np.testing.assert_allclose(z[0]["res"][:, 3:], z[1]["res"][:, 3:], rtol=1e-6)  # reduced metrics agree on all ranks
-    # oracle: W replicas, each loss / W on its own shard, gradients summed, one Adam
-    w0 = b200xf.Transformer(**HP, seed=2).get_weights_dict()
-    oracle = O.OracleTransformer(**HP).load(w0); oracle.iterations = 500
-    for step in range(3):
-        glob = b200xf.synthetic_batch(4 * world, 20, 18, 203, 157, seed=70 + step, ragged=True)
-        shards = [(glob[0][4 * r:4 * r + 4], glob[1][4 * r:4 * r + 4]) for r in range(world)]
-        probe = [O.OracleTransformer(**HP).load({k: p.detach().numpy() for k, p in oracle.params.items()}) for _ in range(world)]
+def _oracle_run(world):
+    w0 = b200xf.Transformer(**HP2, seed=2).get_weights_dict()
+    oracle = O.OracleTransformer(**HP2).load(w0); oracle.iterations = 500
+    per_step = []
+    for step in range(STEPS2):
+        glob = b200xf.synthetic_batch(B2 * world, S2, T2 + 1, 5000, 5000, seed=70 + step, ragged=True)
+        shards = [(glob[0][B2 * r:B2 * (r + 1)], glob[1][B2 * r:B2 * (r + 1)]) for r in range(world)]
         losses, grads = [], None
-        for r in range(world):
-            probe[r].iterations = oracle.iterations
-            l, _, g = O.train_step(probe[r], *shards[r], workers_count=world)
+        for r in range(world):  # W replicas, each loss / W on its own shard (transformer_model.py:16-17), gradients SUMmed
+            probe = O.OracleTransformer(**HP2).load({k: p.detach().numpy() for k, p in oracle.params.items()})
+            probe.iterations = oracle.iterations
+            l, _, g = O.train_step(probe, *shards[r], workers_count=world)
             losses.append(l); grads = g if grads is None else {k: grads[k] + g[k] for k in g}
         O.train_step(oracle, *shards[0], workers_count=world, allreduce=lambda _g: grads)
-        assert abs(z[0]["res"][step, 3] - sum(losses)) < 2e-2          # strategy.reduce(SUM, per-replica losses)
-        assert abs(z[0]["res"][step, 0] - losses[0]) < 2e-2
+        per_step.append(losses)
+    return w0, oracle, grads, per_step
+
+
+MODES = [pytest.param({}, id="default-sharded-pipelined-trailing"), pytest.param({"B200XF_PIPELINED_UPDATE": "1"}, id="pipelined-all"),
+         pytest.param({"B200XF_PIPELINED_UPDATE": "0"}, id="sharded-chained"), pytest.param({"B200XF_SHARDED_UPDATE": "0"}, id="replicated-allreduce")]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+@pytest.mark.parametrize("env", MODES)
+def test_two_ranks_match_oracle_and_each_other(tmp_path, env):
+    import torch.multiprocessing as mp
+    world = 2
+    env = dict(env, B200XF_BUCKET_MB="1")
+    mp.spawn(_rank_main, args=(world, _free_port(), str(tmp_path), env), nprocs=world, join=True)
+    z = [np.load(tmp_path / f"rank{r}.npz") for r in range(world)]
+    names = [k for k in z[0].files if k[:2] in ("w|", "m|", "v|")]
+    for k in names:  # mirrored variables and (after the gather) optimizer slots: identical on every replica
+        assert np.array_equal(z[1][k], z[0][k]), k
+    np.testing.assert_allclose(z[0]["res"][:, 3:], z[1]["res"][:, 3:], rtol=1e-6)  # reduced metrics agree on all ranks
+    assert not np.array_equal(z[0]["mask"], z[1]["mask"])                          # independent dropout masks per replica
+    w0, oracle, grads, per_step = _oracle_run(world)
+    for step, losses in enumerate(per_step):
+        assert abs(z[0]["res"][step, 3] - sum(losses)) < 2e-2          # strategy.reduce(SUM, per-replica losses), __main__.py:131-132
+        assert abs(z[0]["res"][step, 0] - losses[0]) < 2e-2 and abs(z[1]["res"][step, 0] - losses[1]) < 2e-2
     num = den = 0.0
     for k, p in oracle.params.items():
-        ref = p.detach().numpy() - w0[k]; got = z[0][k.replace("/", "|")] - w0[k]
+        ref = p.detach().numpy() - w0[k]; got = z[0]["w|" + k.replace("/", "|")] - w0[k]
         sel = np.abs(grads[k]) > 1e-7
         num += float(np.sum((got[sel] - ref[sel]) ** 2)); den += float(np.sum(ref[sel] ** 2))
-    assert np.sqrt(num / den) < 0.2, np.sqrt(num / den)  # delta-w rel-L2 (bf16 compute vs fp32 oracle, 3 early-Adam steps)
+    assert np.sqrt(num / den) < 0.2, np.sqrt(num / den)  # delta-w rel-L2 (bf16 compute vs fp32 oracle, early-Adam steps)
+    # Adam's first moment against the oracle's (fp32 sums of bf16-computed gradients): whole-state rel-L2
+    mn = np.sqrt(sum(float(np.sum((z[0]["m|" + k.replace("/", "|")] - oracle.m[k]) ** 2)) for k in oracle.m))
+    md = np.sqrt(sum(float(np.sum(oracle.m[k] ** 2)) for k in oracle.m))
+    assert mn / md < 6e-2, mn / md
