@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--hbm-gb", type=float, default=150.0, help="long configuration: device memory the batch is sized to (BASELINE.json configs[4]: ~150 GB)")
     ap.add_argument("--no-allreduce-probe", action="store_true")
     ap.add_argument("--ragged", action="store_true", help="padded batches (lengths U{L/2..L}) instead of full-length ones")
     return ap.parse_args()
@@ -455,6 +456,31 @@ def allreduce_block(model, hp, B, S, T, world, rank, dist, ms_per_step, n_params
     return out
 
 
+def long_batch_for(cfg, budget_bytes):
+    """The long-sequence configuration's batch (BASELINE.json configs[4]: sized to ~150 GB of HBM per GPU) from the library's
+    own memory model: 18 B per parameter of state + the activation / scratch arena for B x (T+1) tokens per side."""
+    import ctypes as C
+    from b200xf import _lib
+    lib = _lib.load()
+
+    def need(B):
+        hp = _lib.HParams(layers_count=cfg["layers_count"], embedding_size=cfg["embedding_size"], heads_count=cfg["heads_count"],
+                          feed_forward_hidden_size=cfg["feed_forward_hidden_size"], input_vocabulary_size=cfg["input_vocabulary_size"],
+                          target_vocabulary_size=cfg["target_vocabulary_size"], maximum_input_length=max(1000, cfg["S"]),
+                          maximum_target_length=max(1000, cfg["T"] + 1), droput_rate=0.0, adam_beta_1=0.9, adam_beta_2=0.98, adam_epsilon=1e-9,
+                          warmup_steps=4000, max_tokens=B * (cfg["T"] + 1))
+        a, b = C.c_int64(), C.c_int64()
+        _lib.check(lib.b200xf_device_bytes(C.byref(hp), C.byref(a), C.byref(b)))
+        return a.value, b.value
+    B = 16
+    while sum(need(B + 16)) <= budget_bytes:
+        B += 16
+    st, ws = need(B)
+    return B, {"budget_gb": budget_bytes / 1e9, "sentences_per_gpu": B, "state_gb": st / 1e9, "workspace_gb": ws / 1e9,
+               "gb_per_sentence": (need(B)[1] - need(B - 16)[1]) / 16 / 1e9,
+               "model": "b200xf_device_bytes: 18 B/parameter (fp32 weights, gradients, Adam m, v, bf16 copy) + arena(max_tokens = B x 1025)"}
+
+
 # ---------------------------------------------------------------------------------------------- main arm
 def main():
     args = parse()
@@ -474,7 +500,12 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     cfg = dict(b200xf.CONFIGS[args.config])
-    B = args.batch or cfg["B"]; S, T = cfg["S"], cfg["T"]
+    S, T = cfg["S"], cfg["T"]
+    B = args.batch or cfg["B"]
+    memory_model = None
+    if args.config == "long" and not args.batch:
+        B, memory_model = long_batch_for(cfg, args.hbm_gb * 1e9)
+    cfg["B"] = B
     hp = dict(layers_count=cfg["layers_count"], embedding_size=cfg["embedding_size"], heads_count=cfg["heads_count"],
               feed_forward_hidden_size=cfg["feed_forward_hidden_size"], input_vocabulary_size=cfg["input_vocabulary_size"],
               target_vocabulary_size=cfg["target_vocabulary_size"], maximum_input_length=max(1000, S), maximum_target_length=max(1000, T + 1),
@@ -561,13 +592,17 @@ def main():
             "step_tflops_achieved_per_gpu": flops_step / (ms / Ksteps / 1e3) / 1e12,
             "step_frac_of_gemm_roofline": (flops_step / (ms / Ksteps / 1e3)) / (peak_sust * 1e12),
             "step_frac_of_nominal_2250tf": (flops_step / (ms / Ksteps / 1e3)) / 2.25e15, "peak_source": peak_src}
+    if memory_model is not None:
+        line["memory_model"] = memory_model
+        line["device_memory_allocated_gb"] = torch.cuda.mem_get_info()[1] / 1e9 - torch.cuda.mem_get_info()[0] / 1e9
     if parity is not None:
         line["parity"] = parity
     if allreduce is not None:
         line["allreduce"] = allreduce
     model.close()
     if not args.no_roofline:
-        gflops, gms, nl = gemm_roofline(cfg, B * S, B * T)
+        rB = min(B, 64) if args.config == "long" else B   # long: the isolated replays use 64 sentences (65 536 tokens) per launch set
+        gflops, gms, nl = gemm_roofline(cfg, rB * S, rB * T)
         ach = gflops / (gms / 1e3) / 1e12
         line["roofline"] = {"bound": "tensor", "kernel": "b200xf::gemm_kernel (tcgen05)", "achieved": ach, "peak": peak_burst, "unit": "TFLOP/s", "frac": ach / peak_burst,
                             "traffic": None, "launches_per_step": nl, "avg_launch_us": gms * 1e3 / nl, "flops_per_launch": gflops / nl,
@@ -582,7 +617,9 @@ def main():
                                            "gemm_share_of_step": ibusy_ms / (ms / Ksteps), "peak_kind": "sustained (kernels timed inside a long step)",
                                            "how": "%globaltimer stamps written by every GEMM CTA of one graph-replayed train step; a launch lasts from its median "
                                                   "CTA's dependency-resolved stamp to its last CTA's exit; weight-gradient GEMMs run concurrently on a side stream, so the sum can exceed their share of the wall clock"}
-        line["roofline"]["secondary"] = secondary_rooflines(cfg, B * T, n_params, peak_hbm)
+        if rB != B:
+            line["roofline"]["note"] = f"isolated replays at {rB} sentences ({rB * T} tokens) per launch set; the timed step runs {B} sentences"
+        line["roofline"]["secondary"] = secondary_rooflines(cfg, rB * T, n_params, peak_hbm)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_block(args.config, cfg, quick=args.steps < 50)
     print(json.dumps(line), flush=True)

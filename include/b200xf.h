@@ -54,6 +54,11 @@ long long b200xf_launch_count(void);
 int b200xf_ctx_create(const b200xf_hparams* hp, int device, void* cuda_stream, b200xf_ctx** out);
 int b200xf_ctx_destroy(b200xf_ctx* ctx);
 
+/* Device memory a context with these hyper-parameters allocates (nothing is allocated by this call): state_bytes = 18 bytes
+ * per parameter (fp32 weights, gradients, Adam m and v, bf16 operand copy), workspace_bytes = the activation / scratch arena
+ * for max_tokens tokens per side.  The memory model behind the batch size of the long-sequence configuration. */
+int b200xf_device_bytes(const b200xf_hparams* hparams, int64_t* state_bytes, int64_t* workspace_bytes);
+
 /* model.trainable_variables / load_weights / save_weights (__main__.py:87,112-114; checkpoint.py:86):
  * the variables live in one flat fp32 device buffer; entry i is a [rows, cols] view (cols == 1-D length
  * for vectors, rows == 1) at element `offset` with row pitch `ld`.  Names are the Keras object-graph keys
@@ -155,6 +160,21 @@ int b200xf_gemm_bf16(const void* a, int lda, int a_mn, const void* b, int ldb, i
                      int accumulate, int M, int N, int K, const float* bias, int relu, const void* resid, int ldr,
                      int resid_op, float alpha, int force_bn, int split_k, void* stream);
 
+/* One sub-layer tail of EncoderLayer / DecoderLayer.call (transformer_model.py:196-198,202-204,232-233,238-240,244-246):
+ *   z = resid + (x W + bias)   (bf16, kept for the backward pass),   y = LayerNormalization(epsilon)(z)
+ * as ONE tcgen05 GEMM whose epilogue normalises: the CTAs holding a 128-row block's column tiles form a thread-block
+ * cluster and exchange per-row partial statistics through distributed shared memory.  x [rows, d_in] bf16, w [d_in, d_out]
+ * bf16 (Keras kernel layout), z / y [rows, d_out] bf16, mean / rstd fp32 [rows]; d_out a multiple of 8, at most 2048. */
+int b200xf_dense_layernorm_fwd(const void* x, int ldx, const void* w, int ldw, const float* bias, const void* resid, int ldr,
+                               void* z, int ldz, const float* gamma, const float* beta, void* y, int ldy, float* mean,
+                               float* rstd, int rows, int d_out, int d_in, float eps, void* stream);
+/* Both parameter gradients of a Dense layer (tape.gradient at __main__.py:112) from one pass over dy:
+ *   dw[d_in, d_out] += x^T dy (fp32, accumulated),   dbias[d_out] = sum over tokens of dy
+ * the column sums are taken from the dy tiles the weight-gradient GEMM stages in shared memory anyway.  scratch: fp32
+ * DEVICE buffer of at least 148 * d_out floats (one partial row per K split and row block of the weight). */
+int b200xf_dense_wgrad_bias(const void* x, int ldx, const void* dy, int lddy, float* dw, int lddw, float* dbias, float* scratch,
+                            size_t scratch_floats, int tokens, int d_in, int d_out, void* stream);
+
 /* Debug aid (no counterpart in the reference): when given a DEVICE buffer of 8 * 148 uint64, every later GEMM launch
  * records %globaltimer stamps per CTA (start, set-up done, first operands landed, last MMA issued, accumulator ready,
  * epilogue done, exit).  Pass NULL to switch it off. */
@@ -218,6 +238,13 @@ int b200xf_embed_pe_bwd(const int64_t* tokens, const void* dx, float* dtable, in
  * scratch: rows * 8 + 16 bytes. */
 int b200xf_vocab_ce_fwd_bwd(void* logits, int ldl, const int64_t* labels, int rows, int V, int workers_count,
                             int write_grad, float* out3, void* scratch, void* stream);
+
+/* local_loss_function / accuracy_function (transformer_model.py:11-26) on fp32 logits as Transformer.call returns them:
+ * PAD-masked sparse softmax cross-entropy / (non-pad count * workers_count) and the masked argmax accuracy counts, computed
+ * in fp32 from the fp32 logits (nothing is rounded to bf16), no gradient.  out3 = {loss, accuracy numerator, denominator};
+ * scratch: (2 * rows + 64) * 4 bytes. */
+int b200xf_vocab_ce_f32(const float* logits, int ldl, const int64_t* labels, int rows, int V, int workers_count, float* out3,
+                        void* scratch, void* stream);
 
 /* tf.keras.optimizers.Adam(TransformerLearningRateSchedule(d), beta_1, beta_2, epsilon) applied to a flat range
  * (__main__.py:56-73,113-114).  iterations_dev: DEVICE int64 holding optimizer.iterations before the step. */

@@ -9,14 +9,14 @@ from .batching import BatchAssembler, pad_to_longest, padded_length, ragged_to_f
 from .cluster import B200Cluster, launch
 from .synthetic import CONFIGS, step_flops, synthetic_batch
 from .training import (Adam, B200Strategy, CustomSchedule, Mean, ReduceOp, StepResult, TransformerLearningRateSchedule,
-                       make_distributed_train_step, make_test_step, make_train_step)
+                       make_distributed_test_step, make_distributed_train_step, make_test_step, make_train_step)
 from .transformer_model import (AttentionWeights, Transformer, accuracy_function, build_model, greedy_decode, create_look_ahead_mask, create_padding_mask,
                                 local_loss_function, loss_function, positional_encoding)
 
 __all__ = [
     "Transformer", "AttentionWeights", "greedy_decode", "build_model", "local_loss_function", "loss_function", "accuracy_function", "positional_encoding",
     "create_padding_mask", "create_look_ahead_mask", "TransformerLearningRateSchedule", "CustomSchedule", "Adam",
-    "B200Strategy", "ReduceOp", "Mean", "StepResult", "make_train_step", "make_distributed_train_step", "make_test_step",
+    "B200Strategy", "ReduceOp", "Mean", "StepResult", "make_train_step", "make_distributed_train_step", "make_distributed_test_step", "make_test_step",
     "synthetic_batch", "step_flops", "CONFIGS", "B200XFError", "LIB_PATH",
     "BatchAssembler", "pad_to_longest", "padded_length", "ragged_to_flat", "replica_rows", "B200Cluster", "launch",
 ]

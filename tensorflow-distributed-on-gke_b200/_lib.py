@@ -41,6 +41,7 @@ SIGNATURES = {
     "b200xf_launch_count": (C.c_longlong, []),
     "b200xf_ctx_create": (_I, [C.POINTER(HParams), _I, _P, C.POINTER(_P)]),
     "b200xf_ctx_destroy": (_I, [_P]),
+    "b200xf_device_bytes": (_I, [C.POINTER(HParams), C.POINTER(_L), C.POINTER(_L)]),
     "b200xf_param_count": (_I, [_P]),
     "b200xf_param_info": (_I, [_P, _I, C.c_char_p, _SZ, C.POINTER(_L), C.POINTER(_L), C.POINTER(_L), C.POINTER(_L), C.POINTER(C.c_int32)]),
     "b200xf_param_total": (_L, [_P]),
@@ -68,6 +69,8 @@ SIGNATURES = {
     "b200xf_optimizer_state_complete": (_I, [_P]),
     "b200xf_allreduce_bucket": (_I, [_P, _P, _L]),
     "b200xf_gemm_bf16": (_I, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _I, _I, _I, _P, _I, _P, _I, _I, _F, _I, _I, _P]),
+    "b200xf_dense_layernorm_fwd": (_I, [_P, _I, _P, _I, _P, _P, _I, _P, _I, _P, _P, _P, _I, _P, _P, _I, _I, _I, _F, _P]),
+    "b200xf_dense_wgrad_bias": (_I, [_P, _I, _P, _I, _P, _I, _P, _P, _SZ, _I, _I, _I, _P]),
     "b200xf_assemble_padded": (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),
     "b200xf_debug_gemm_trace": (_I, [_P]),
     "b200xf_debug_gemm_trace_ring": (_I, [_P, _I]),
@@ -82,6 +85,7 @@ SIGNATURES = {
     "b200xf_embed_bwd_scratch_bytes": (_SZ, [_I]),
     "b200xf_embed_pe_bwd": (_I, [_P, _P, _P, _I, _I, _I, _P, _SZ, _P]),
     "b200xf_vocab_ce_fwd_bwd": (_I, [_P, _I, _P, _I, _I, _I, _I, _P, _P, _P]),
+    "b200xf_vocab_ce_f32": (_I, [_P, _I, _P, _I, _I, _I, _P, _P, _P]),
     "b200xf_adam_step": (_I, [_P, _P, _P, _P, _P, _L, _P, _I, _I, _F, _F, _F, _I, _P]),
     "b200xf_crc32c": (C.c_uint32, [_P, _SZ, C.c_uint32]),
     "b200xf_positional_encoding_host": (_I, [_P, _I, _I]),

@@ -28,6 +28,16 @@ int b200xf_ctx_create(const b200xf_hparams* hp, int device, void* cuda_stream, b
 }
 int b200xf_ctx_destroy(b200xf_ctx* ctx) { delete ctx; return 0; }
 
+int b200xf_device_bytes(const b200xf_hparams* hp, int64_t* state_bytes, int64_t* workspace_bytes) {
+  if (!hp || !state_bytes || !workspace_bytes) return set_error("null argument");
+  Context c;                      // layout only: nothing is allocated
+  c.hp = *hp;
+  c.build_layout();
+  *state_bytes = int64_t(c.total_params) * 18;   // fp32 weights, gradients, Adam m and v + the bf16 operand copy
+  *workspace_bytes = int64_t(Context::arena_bytes_for(*hp, c.vt_ld, nullptr, nullptr));
+  return 0;
+}
+
 int b200xf_param_count(b200xf_ctx* ctx) { return ctx ? int(ctx->c.table.size()) : 0; }
 int b200xf_param_info(b200xf_ctx* ctx, int index, char* name_buf, size_t name_buf_len, int64_t* rows, int64_t* cols, int64_t* ld,
                       int64_t* offset, int32_t* ndim) {
@@ -160,6 +170,34 @@ int b200xf_gemm_bf16(const void* a, int lda, int a_mn, const void* b, int ldb, i
   return gemm_bf16(g, static_cast<cudaStream_t>(stream));
 }
 
+int b200xf_dense_layernorm_fwd(const void* x, int ldx, const void* w, int ldw, const float* bias, const void* resid, int ldr, void* z, int ldz,
+                               const float* gamma, const float* beta, void* y, int ldy, float* mean, float* rstd, int rows, int d_out, int d_in,
+                               float eps, void* stream) {
+  if (!x || !w || !z || !y || !gamma || !beta || !mean || !rstd) return set_error("dense_layernorm_fwd: null pointer");
+  if (!gemm_ln_fusable(rows, d_out)) return set_error("dense_layernorm_fwd: width %d unsupported (multiple of 8, <= 2048)", d_out);
+  GemmArgs g;
+  g.a = x; g.lda = ldx; g.a_mn = 0; g.b = w; g.ldb = ldw; g.b_mn = 1; g.d = z; g.ldd = ldz;
+  g.M = rows; g.N = d_out; g.K = d_in; g.bias = bias; g.resid = resid; g.ldr = ldr; g.resid_op = resid ? 1 : 0;
+  g.ln_gamma = gamma; g.ln_beta = beta; g.ln_y = y; g.ln_ldy = ldy; g.ln_mean = mean; g.ln_rstd = rstd; g.ln_eps = eps;
+  return gemm_bf16(g, static_cast<cudaStream_t>(stream));
+}
+
+int b200xf_dense_wgrad_bias(const void* x, int ldx, const void* dy, int lddy, float* dw, int lddw, float* dbias, float* scratch, size_t scratch_floats,
+                            int tokens, int d_in, int d_out, void* stream) {
+  if (!x || !dy || !dw || !dbias || !scratch) return set_error("dense_wgrad_bias: null pointer");
+  GemmArgs g;
+  g.a = x; g.lda = ldx; g.a_mn = 1; g.b = dy; g.ldb = lddy; g.b_mn = 1; g.d = dw; g.ldd = lddw; g.d_fp32 = 1; g.accumulate = 1;
+  g.M = d_in; g.N = d_out; g.K = tokens;
+  GemmInfo info;
+  B200XF_TRY(gemm_plan(g, &info));
+  const int rows = info.splits * info.tiles_m;
+  if (size_t(rows) * d_out > scratch_floats) return set_error("dense_wgrad_bias: scratch of %zu floats needed", size_t(rows) * d_out);
+  g.colsum_partials = scratch;
+  B200XF_TRY(gemm_bf16(g, static_cast<cudaStream_t>(stream)));
+  ReduceJob job{scratch, dbias, rows, d_out, d_out};
+  return reduce_partials(&job, 1, static_cast<cudaStream_t>(stream));
+}
+
 int b200xf_debug_gemm_trace(void* device_u64_buffer) {
   gemm_set_trace(static_cast<unsigned long long*>(device_u64_buffer));
   return 0;
@@ -248,6 +286,20 @@ int b200xf_vocab_ce_fwd_bwd(void* logits, int ldl, const int64_t* labels, int ro
   const float inv_w = 1.0f / float(workers_count);
   B200XF_TRY(vocab_ce_fwd_bwd(static_cast<bf16*>(logits), ldl, lab, rows, V, count, inv_w, row_loss, row_correct, write_grad, s));
   return ce_finalize(row_loss, row_correct, count, rows, inv_w, out3, s);
+}
+
+int b200xf_vocab_ce_f32(const float* logits, int ldl, const int64_t* labels, int rows, int V, int workers_count, float* out3, void* scratch,
+                        void* stream) {
+  if (!logits || !labels || !scratch || !out3 || workers_count <= 0) return set_error("vocab_ce_f32: bad argument");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  float* row_loss = static_cast<float*>(scratch);
+  int* row_correct = reinterpret_cast<int*>(row_loss + rows);
+  int* count = row_correct + rows;
+  const long long* lab = reinterpret_cast<const long long*>(labels);
+  count_nonpad_kernel<<<1, 1024, 0, s>>>(lab, rows, count);
+  count_launch();
+  B200XF_TRY(vocab_ce_f32(logits, ldl, lab, rows, V, row_loss, row_correct, s));
+  return ce_finalize(row_loss, row_correct, count, rows, 1.0f / float(workers_count), out3, s);
 }
 
 int b200xf_adam_step(float* w, float* g, float* m, float* v, void* w_bf16, int64_t n, const int64_t* iterations_dev, int embedding_size,

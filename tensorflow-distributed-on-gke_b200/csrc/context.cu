@@ -216,6 +216,46 @@ int Context::arena_alloc(T** out, size_t count) {
   return 0;
 }
 
+// Bytes of the activation / workspace arena for `max_tokens` tokens per side (the memory model behind the batch sizes of the
+// long-sequence configuration: see b200xf_device_bytes).
+size_t Context::arena_bytes_for(const b200xf_hparams& hp, int vt_ld, size_t* red_capacity_out, size_t* emb_scratch_out) {
+  const int L = hp.layers_count, d = hp.embedding_size, H = hp.heads_count, dff = hp.feed_forward_hidden_size;
+  const size_t N = size_t(hp.max_tokens);
+  const size_t nd = N * d, nff = N * dff;
+  size_t red_capacity = 0;
+  // column-sum partials of one backward pass: 5L LayerNorms, per-layer QKV / FFN1 / (Q2) bias sums, K|V and vocab bias sums
+  {
+    const int n = int(N);
+    size_t f = size_t(5 * L) * (ln_bwd_scratch_floats(n, d) + 64);
+    f += size_t(2 * L) * (size_t(colsum_parts(n, 3 * d)) * 3 * d + 64) + size_t(2 * L) * (size_t(colsum_parts(n, dff)) * dff + 64);
+    f += size_t(L) * (size_t(colsum_parts(n, d)) * d + 64) + size_t(colsum_parts(n, L * 2 * d)) * L * 2 * d + 64;
+    f += size_t(colsum_parts(n, hp.target_vocabulary_size)) * hp.target_vocabulary_size + 64;
+    red_capacity = f + 4096;
+  }
+  const size_t emb_scratch_bytes = embed_bwd_scratch_bytes(int(N));
+  size_t bytes = 0;
+  auto need = [&](size_t count, size_t elt) { bytes += align_up(count * elt, 256); };
+  // encoder: x (L+1), qkv, ctx, z1, o1, h, z2, lse, 4 stats
+  need(nd * (L + 1), 2);
+  for (int l = 0; l < L; ++l) { need(3 * nd, 2); need(nd, 2); need(nd, 2); need(nd, 2); need(nff, 2); need(nd, 2); need(2 * N * H, 4); need(4 * N, 4); }
+  // decoder: x (L+1), qkv, ctx1, z1, o1, q2, ctx2, z2, o2, h, z3, lse1, lse2, 6 stats
+  need(nd * (L + 1), 2);
+  for (int l = 0; l < L; ++l) { need(3 * nd, 2); for (int i = 0; i < 8; ++i) need(nd, 2); need(nff, 2); need(4 * N * H, 4); need(6 * N, 4); }
+  need(N * size_t(L) * 2 * d, 2); need(N * size_t(L) * 2 * d, 2);   // kv_all, dkv_all
+  need(N * size_t(vt_ld), 2);                                       // logits / dlogits
+  for (int i = 0; i < 9; ++i) need(nd, 2);                          // dA dB dctx, 2 x (dz dzm dq2)
+  need(2 * nff, 2); need(2 * 3 * nd, 2);                            // 2 x dh, 2 x dqkv
+  need(N * H, 4); need(nd, 4);                                      // delta, fp32 dQ accumulator
+  for (int i = 0; i < 4; ++i) need(N + 64, 8);                      // inp, target, tgt_in, labels
+  need(N, 4); need(N, 4);                                           // row_loss, row_correct
+  need(red_capacity, 4); need(emb_scratch_bytes, 1);
+  need(size_t(hp.maximum_input_length) * d, 4); need(size_t(hp.maximum_target_length) * d, 4);
+  need(1024, 1);
+  if (red_capacity_out) *red_capacity_out = red_capacity;
+  if (emb_scratch_out) *emb_scratch_out = emb_scratch_bytes;
+  return bytes + (1 << 20);
+}
+
 int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   hp = h; device = dev; user_stream = s;
   const int L = hp.layers_count, d = hp.embedding_size, H = hp.heads_count, dff = hp.feed_forward_hidden_size;
@@ -251,35 +291,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   // ---- workspace arena
   const size_t N = size_t(hp.max_tokens);
   const size_t nd = N * d, nff = N * dff;
-  // column-sum partials of one backward pass: 5L LayerNorms, per-layer QKV / FFN1 / (Q2) bias sums, K|V and vocab bias sums
-  {
-    const int n = int(N);
-    size_t f = size_t(5 * L) * (ln_bwd_scratch_floats(n, d) + 64);
-    f += size_t(2 * L) * (size_t(colsum_parts(n, 3 * d)) * 3 * d + 64) + size_t(2 * L) * (size_t(colsum_parts(n, dff)) * dff + 64);
-    f += size_t(L) * (size_t(colsum_parts(n, d)) * d + 64) + size_t(colsum_parts(n, L * 2 * d)) * L * 2 * d + 64;
-    f += size_t(colsum_parts(n, hp.target_vocabulary_size)) * hp.target_vocabulary_size + 64;
-    red_capacity = f + 4096;
-  }
-  emb_scratch_bytes = embed_bwd_scratch_bytes(int(N));
-  size_t bytes = 0;
-  auto need = [&](size_t count, size_t elt) { bytes += align_up(count * elt, 256); };
-  // encoder: x (L+1), qkv, ctx, z1, o1, h, z2, lse, 4 stats
-  need(nd * (L + 1), 2);
-  for (int l = 0; l < L; ++l) { need(3 * nd, 2); need(nd, 2); need(nd, 2); need(nd, 2); need(nff, 2); need(nd, 2); need(2 * N * H, 4); need(4 * N, 4); }
-  // decoder: x (L+1), qkv, ctx1, z1, o1, q2, ctx2, z2, o2, h, z3, lse1, lse2, 6 stats
-  need(nd * (L + 1), 2);
-  for (int l = 0; l < L; ++l) { need(3 * nd, 2); for (int i = 0; i < 8; ++i) need(nd, 2); need(nff, 2); need(4 * N * H, 4); need(6 * N, 4); }
-  need(N * size_t(L) * 2 * d, 2); need(N * size_t(L) * 2 * d, 2);   // kv_all, dkv_all
-  need(N * size_t(vt_ld), 2);                                       // logits / dlogits
-  for (int i = 0; i < 9; ++i) need(nd, 2);                          // dA dB dctx, 2 x (dz dzm dq2)
-  need(2 * nff, 2); need(2 * 3 * nd, 2);                            // 2 x dh, 2 x dqkv
-  need(N * H, 4); need(nd, 4);                                      // delta, fp32 dQ accumulator
-  for (int i = 0; i < 4; ++i) need(N + 64, 8);                      // inp, target, tgt_in, labels
-  need(N, 4); need(N, 4);                                           // row_loss, row_correct
-  need(red_capacity, 4); need(emb_scratch_bytes, 1);
-  need(size_t(hp.maximum_input_length) * d, 4); need(size_t(hp.maximum_target_length) * d, 4);
-  need(1024, 1);
-  arena_size = bytes + (1 << 20);
+  arena_size = arena_bytes_for(hp, vt_ld, &red_capacity, &emb_scratch_bytes);
   B200XF_CUDA(cudaMalloc(&arena, arena_size));
   B200XF_CUDA(cudaMemsetAsync(arena, 0, arena_size, stream));
   arena_used = 0;
@@ -345,6 +357,9 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
   if (const char* e = getenv("B200XF_SIDE_WGRAD")) side_on = atoi(e) != 0;
+  if (const char* e = getenv("B200XF_FUSE_LN")) fuse_ln = atoi(e);
+  if (const char* e = getenv("B200XF_FUSE_COLSUM")) fuse_colsum = atoi(e);
+  if (const char* e = getenv("B200XF_FUSE_MIN_TOKENS")) fuse_min_tokens = std::max(0, atoi(e));
   if (const char* e = getenv("B200XF_PHASE_TIMING")) phase_timing = atoi(e) != 0;
   if (const char* e = getenv("B200XF_GRAPH")) use_graph = atoi(e) != 0;
   if (const char* e = getenv("B200XF_SHARDED_UPDATE")) sharded_update = std::max(0, std::min(2, atoi(e)));
@@ -363,6 +378,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
 }
 
 Context::~Context() {
+  if (!stream && !params && !arena) return;  // never initialised (layout-only use): nothing on any device to release
   drop_graphs();
   if (phase_timing && phase_n > 0)
     fprintf(stderr, "[b200xf] phases over %ld steps (ms): forward %.3f  loss %.3f  backward %.3f  update+join %.3f\n", phase_n,
@@ -525,13 +541,43 @@ int Context::dense_dgrad(const bf16* dy, int M, const Dense& p, bf16* dx, const 
   g.max_ctas = backward_gemm_cap();
   return gemm_bf16(g, stream);
 }
-int Context::dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p) {
+int Context::dense_ln_fwd(const bf16* x, int M, const Dense& p, bf16* z, const bf16* resid, int drop_site, const LnP& ln, bf16* y,
+                          float* mean, float* rstd) {
+  const float eps = 1e-6f;  // transformer_model.py:187-188
+  if (!fused(fuse_ln, M) || !gemm_ln_fusable(M, p.N)) {
+    B200XF_TRY(dense_fwd(x, M, p, z, 0, resid, drop_site));
+    return layernorm_fwd(z, nullptr, params + ln.g, params + ln.b, y, nullptr, mean, rstd, M, p.N, eps, stream);
+  }
+  GemmArgs g;
+  g.a = x; g.lda = p.K; g.a_mn = 0;
+  g.b = shadow + p.w; g.ldb = p.ld; g.b_mn = 1;
+  g.d = z; g.ldd = p.ld; g.d_fp32 = 0;
+  g.M = M; g.N = p.N; g.K = p.K;
+  g.bias = params + p.b;
+  g.resid = resid; g.ldr = p.ld; g.resid_op = resid ? 1 : 0;
+  if (drop_site >= 0) g.drop = site_drop(drop_site);
+  g.b_static = weights_static & 1;
+  g.ln_gamma = params + ln.g; g.ln_beta = params + ln.b; g.ln_y = y; g.ln_ldy = p.N; g.ln_mean = mean; g.ln_rstd = rstd; g.ln_eps = eps;
+  return gemm_bf16(g, stream);
+}
+
+int Context::dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p, bool bias_grad) {
+  if (bias_grad && !fused(fuse_colsum, M)) { B200XF_TRY(colsum(dy, p.ld, M, p.N, p.b)); bias_grad = false; }
   GemmArgs g;
   g.a = x; g.lda = p.K; g.a_mn = 1;    // X [tokens][K]  == A stored [contract][M=K]
   g.b = dy; g.ldb = p.ld; g.b_mn = 1;  // dY [tokens][N] == B stored [contract][N]
   g.d = grads + p.w; g.ldd = p.ld; g.d_fp32 = 1; g.accumulate = 1;
   g.M = p.K; g.N = p.N; g.K = M;
   g.max_ctas = backward_gemm_cap();
+  if (bias_grad) {
+    GemmInfo info;
+    B200XF_TRY(gemm_plan(g, &info));
+    const int rows = info.splits * info.tiles_m;   // one partial row per (K split, row block of the weight)
+    float* part = red_alloc(size_t(rows) * p.N);
+    if (!part) return set_error("reduction scratch exhausted");
+    g.colsum_partials = part;
+    red_jobs.push_back({part, grads + p.b, rows, p.N, p.N});
+  }
   cudaStream_t s;
   B200XF_TRY(side_launch_begin(&s));
   // No operand prefetch here: dy arrives over the fork event, and a launch with the programmatic attribute may begin
@@ -558,7 +604,6 @@ int Context::forward(const long long* inp, const long long* tgt_in, int B, int S
   const int L = hp.layers_count, d = hp.embedding_size, H = hp.heads_count, dk = d / H;
   const int Ns = B * S, Nt = B * T;
   const size_t cap = size_t(hp.max_tokens) * d;
-  const float eps = 1e-6f;  // transformer_model.py:187-188
 
   // ---- encoder (transformer_model.py:270-279)
   B200XF_TRY(embed_pe_fwd(inp, params + enc_emb, hp.input_vocabulary_size, pe_in, enc_x, B, S, d, stream, site_drop(0)));
@@ -572,11 +617,9 @@ int Context::forward(const long long* inp, const long long* tgt_in, int B, int S
     at.o = a.ctx; at.ldo = d; at.lse = a.lse; at.key_tokens = inp; at.causal = 0;
     at.B = B; at.H = H; at.Sq = S; at.Sk = S; at.dk = dk;
     B200XF_TRY(attention_fwd(at, stream));
-    B200XF_TRY(dense_fwd(a.ctx, Ns, w.o, a.z1, 0, x, 2 + 2 * l));                        // z1 = x + drop(mha(x))
-    B200XF_TRY(layernorm_fwd(a.z1, nullptr, params + w.ln1.g, params + w.ln1.b, a.o1, nullptr, st, st + Ns, Ns, d, eps, stream));
+    B200XF_TRY(dense_ln_fwd(a.ctx, Ns, w.o, a.z1, x, 2 + 2 * l, w.ln1, a.o1, st, st + Ns));          // z1 = x + drop(mha(x)); o1 = LN1(z1)
     B200XF_TRY(dense_fwd(a.o1, Ns, w.f1, a.h, 1, nullptr));
-    B200XF_TRY(dense_fwd(a.h, Ns, w.f2, a.z2, 0, a.o1, 3 + 2 * l));                      // z2 = o1 + drop(ffn(o1))
-    B200XF_TRY(layernorm_fwd(a.z2, nullptr, params + w.ln2.g, params + w.ln2.b, out, nullptr, st + 2 * Ns, st + 3 * Ns, Ns, d, eps, stream));
+    B200XF_TRY(dense_ln_fwd(a.h, Ns, w.f2, a.z2, a.o1, 3 + 2 * l, w.ln2, out, st + 2 * Ns, st + 3 * Ns));  // z2 = o1 + drop(ffn(o1)); out = LN2(z2)
   }
   const bf16* enc_out = enc_x + size_t(L) * cap;
   B200XF_TRY(dense_fwd(enc_out, Ns, kv_all, kv, 0, nullptr));  // K|V of every decoder layer's cross-attention
@@ -593,8 +636,7 @@ int Context::forward(const long long* inp, const long long* tgt_in, int B, int S
     s1.o = a.ctx1; s1.ldo = d; s1.lse = a.lse1; s1.key_tokens = tgt_in; s1.causal = 1;
     s1.B = B; s1.H = H; s1.Sq = T; s1.Sk = T; s1.dk = dk;
     B200XF_TRY(attention_fwd(s1, stream));
-    B200XF_TRY(dense_fwd(a.ctx1, Nt, w.o1, a.z1, 0, x, 2 + 2 * L + 3 * l));
-    B200XF_TRY(layernorm_fwd(a.z1, nullptr, params + w.ln1.g, params + w.ln1.b, a.o1, nullptr, st, st + Nt, Nt, d, eps, stream));
+    B200XF_TRY(dense_ln_fwd(a.ctx1, Nt, w.o1, a.z1, x, 2 + 2 * L + 3 * l, w.ln1, a.o1, st, st + Nt));
     B200XF_TRY(dense_fwd(a.o1, Nt, w.q2, a.q2, 0, nullptr));
     AttnArgs c2;
     c2.q = a.q2; c2.ldq = d; c2.k = kv + size_t(l) * 2 * d; c2.v = kv + size_t(l) * 2 * d + d; c2.ldk = c2.ldv = kv_all.ld;
@@ -602,11 +644,9 @@ int Context::forward(const long long* inp, const long long* tgt_in, int B, int S
     c2.B = B; c2.H = H; c2.Sq = T; c2.Sk = S; c2.dk = dk;
     c2.early = (weights_static & 2) ? 2 : 0;  // K|V of all layers were projected right after the encoder
     B200XF_TRY(attention_fwd(c2, stream));
-    B200XF_TRY(dense_fwd(a.ctx2, Nt, w.o2, a.z2, 0, a.o1, 3 + 2 * L + 3 * l));
-    B200XF_TRY(layernorm_fwd(a.z2, nullptr, params + w.ln2.g, params + w.ln2.b, a.o2, nullptr, st + 2 * Nt, st + 3 * Nt, Nt, d, eps, stream));
+    B200XF_TRY(dense_ln_fwd(a.ctx2, Nt, w.o2, a.z2, a.o1, 3 + 2 * L + 3 * l, w.ln2, a.o2, st + 2 * Nt, st + 3 * Nt));
     B200XF_TRY(dense_fwd(a.o2, Nt, w.f1, a.h, 1, nullptr));
-    B200XF_TRY(dense_fwd(a.h, Nt, w.f2, a.z3, 0, a.o2, 4 + 2 * L + 3 * l));
-    B200XF_TRY(layernorm_fwd(a.z3, nullptr, params + w.ln3.g, params + w.ln3.b, out, nullptr, st + 4 * Nt, st + 5 * Nt, Nt, d, eps, stream));
+    B200XF_TRY(dense_ln_fwd(a.h, Nt, w.f2, a.z3, a.o2, 4 + 2 * L + 3 * l, w.ln3, out, st + 4 * Nt, st + 5 * Nt));
   }
   const bf16* dec_out = dec_x + size_t(L) * cap;
   // ---- final_layer (transformer_model.py:347)
@@ -695,8 +735,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
   red_used = 0; red_jobs.clear();
 
   const bf16* dec_out = dec_x + size_t(L) * cap;
-  B200XF_TRY(dense_wgrad(dec_out, logits, Nt, final_layer));
-  B200XF_TRY(colsum(logits, final_layer.ld, Nt, final_layer.N, final_layer.b));
+  B200XF_TRY(dense_wgrad(dec_out, logits, Nt, final_layer, true));
   bf16* cur = dA; bf16* other = dB;
   B200XF_TRY(dense_dgrad(logits, Nt, final_layer, cur, nullptr, 0));
   B200XF_TRY(section_done());
@@ -710,8 +749,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     B200XF_TRY(dense_wgrad(a.h, dsub, Nt, w.f2));
     B200XF_TRY(sb_write(sb_dh, &dh));
     B200XF_TRY(dense_dgrad(dsub, Nt, w.f2, dh, a.h, 2));
-    B200XF_TRY(colsum(dh, w.f1.ld, Nt, w.f1.N, w.f1.b));
-    B200XF_TRY(dense_wgrad(a.o2, dh, Nt, w.f1));
+    B200XF_TRY(dense_wgrad(a.o2, dh, Nt, w.f1, true));
     B200XF_TRY(dense_dgrad(dh, Nt, w.f1, other, dz, 1));
     std::swap(cur, other);
     // LN2 / cross attention
@@ -727,8 +765,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     c2.dk_out = dkv + size_t(l) * 2 * d; c2.dv_out = dkv + size_t(l) * 2 * d + d; c2.lddk = c2.lddv = kv_all.ld; c2.delta = delta; c2.dq_acc = dq_acc;
     c2.early = (weights_static & 2) ? 3 : 0;
     B200XF_TRY(attention_bwd(c2, stream));
-    B200XF_TRY(colsum(dq2, d, Nt, d, w.q2.b));
-    B200XF_TRY(dense_wgrad(a.o1, dq2, Nt, w.q2));
+    B200XF_TRY(dense_wgrad(a.o1, dq2, Nt, w.q2, true));
     B200XF_TRY(dense_dgrad(dq2, Nt, w.q2, other, dz, 1));
     std::swap(cur, other);
     // LN1 / causal self attention
@@ -744,16 +781,14 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     s1.delta = delta; s1.dq_acc = dq_acc;
     s1.early = (weights_static & 2) ? 3 : 0;
     B200XF_TRY(attention_bwd(s1, stream));
-    B200XF_TRY(colsum(dqkv, 3 * d, Nt, 3 * d, w.qkv1.b));
-    B200XF_TRY(dense_wgrad(x, dqkv, Nt, w.qkv1));
+    B200XF_TRY(dense_wgrad(x, dqkv, Nt, w.qkv1, true));
     B200XF_TRY(dense_dgrad(dqkv, Nt, w.qkv1, other, dz, 1));
     std::swap(cur, other);
     B200XF_TRY(section_done());
   }
   B200XF_TRY(embed_bwd(tgt_in, cur, grads + dec_emb, hp.target_vocabulary_size, Nt, d, emb_scratch, emb_scratch_bytes, stream, site_drop(1)));
   const bf16* enc_out = enc_x + size_t(L) * cap;
-  B200XF_TRY(colsum(dkv, kv_all.ld, Ns, kv_all.N, kv_all.b));
-  B200XF_TRY(dense_wgrad(enc_out, dkv, Ns, kv_all));
+  B200XF_TRY(dense_wgrad(enc_out, dkv, Ns, kv_all, true));
   B200XF_TRY(dense_dgrad(dkv, Ns, kv_all, cur, nullptr, 0));
   B200XF_TRY(section_done());
 
@@ -765,8 +800,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     B200XF_TRY(dense_wgrad(a.h, dsub, Ns, w.f2));
     B200XF_TRY(sb_write(sb_dh, &dh));
     B200XF_TRY(dense_dgrad(dsub, Ns, w.f2, dh, a.h, 2));
-    B200XF_TRY(colsum(dh, w.f1.ld, Ns, w.f1.N, w.f1.b));
-    B200XF_TRY(dense_wgrad(a.o1, dh, Ns, w.f1));
+    B200XF_TRY(dense_wgrad(a.o1, dh, Ns, w.f1, true));
     B200XF_TRY(dense_dgrad(dh, Ns, w.f1, other, dz, 1));
     std::swap(cur, other);
     B200XF_TRY(ln_bwd(cur, a.z1, st, st + Ns, w.ln1, w.o.b, Ns, 2 + 2 * l));
@@ -781,8 +815,7 @@ int Context::backward(const long long* inp, const long long* tgt_in, int B, int 
     at.delta = delta; at.dq_acc = dq_acc;
     at.early = (weights_static & 2) ? 3 : 0;
     B200XF_TRY(attention_bwd(at, stream));
-    B200XF_TRY(colsum(dqkv, 3 * d, Ns, 3 * d, w.qkv.b));
-    B200XF_TRY(dense_wgrad(x, dqkv, Ns, w.qkv));
+    B200XF_TRY(dense_wgrad(x, dqkv, Ns, w.qkv, true));
     B200XF_TRY(dense_dgrad(dqkv, Ns, w.qkv, other, dz, 1));
     std::swap(cur, other);
     B200XF_TRY(section_done());

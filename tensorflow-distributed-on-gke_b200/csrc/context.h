@@ -120,6 +120,7 @@ struct Context {
   bool overlap_update = false;
   bool overlap_single = true;   // single GPU too: each bucket's Adam runs on the update stream under the rest of backward (B200XF_OVERLAP_UPDATE=0 disables)
 
+  static size_t arena_bytes_for(const b200xf_hparams& hp, int vt_ld, size_t* red_capacity_out, size_t* emb_scratch_out);
   ~Context();
   int init(const b200xf_hparams& h, int dev, cudaStream_t s);
   void build_layout();
@@ -138,7 +139,17 @@ struct Context {
   int dense_fwd(const bf16* x, int M, const Dense& p, bf16* y, int relu, const bf16* resid, int drop_site = -1);
   DropArgs site_drop(int site) const;
   int dense_dgrad(const bf16* dy, int M, const Dense& p, bf16* dx, const bf16* resid, int resid_op);
-  int dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p);
+  // bias_grad: the weight-gradient GEMM also sums dy's columns (the Dense's bias gradient) from the tiles it stages anyway
+  int dense_wgrad(const bf16* x, const bf16* dy, int M, const Dense& p, bool bias_grad = false);
+  // y = LayerNorm(z), z = resid + drop(x W + b): one GEMM whose epilogue normalises (B200XF_FUSE_LN=0: GEMM, then LayerNorm kernel)
+  int dense_ln_fwd(const bf16* x, int M, const Dense& p, bf16* z, const bf16* resid, int drop_site, const LnP& ln, bf16* y, float* mean, float* rstd);
+  // B200XF_FUSE_LN / B200XF_FUSE_COLSUM: 1 always, 0 never (default), -1 from the batch size (>= B200XF_FUSE_MIN_TOKENS tokens).
+  // Both fused epilogues are correct (tests/test_kernels_gpu.py, tests/test_bench_path_gpu.py run them) and save launches and an
+  // HBM pass, yet measured slower inside the step at every configuration (profiles/r02_fusion_ab.md): the LayerNorm epilogue
+  // is fully exposed behind a one-tile main loop and gives up the persistent kernel's epilogue / main-loop overlap; the column
+  // sums read the staged tiles from shared memory, whose bandwidth the tensor core's own operand reads already use up.
+  int fuse_ln = 0, fuse_colsum = 0, fuse_min_tokens = 16384;
+  bool fused(int mode, int tokens) const { return mode > 0 || (mode < 0 && tokens >= fuse_min_tokens); }
   int ln_bwd(const bf16* dy, const bf16* z, const float* mean, const float* rstd, const LnP& p, size_t dcol_off, int rows, int drop_site);
   int colsum(const bf16* x, int ld, int rows, int cols, size_t dst_off);
   float* red_alloc(size_t floats);

@@ -625,6 +625,49 @@ vocab_ce_kernel(bf16* __restrict__ logits, int ldl, const long long* __restrict_
   }
 }
 
+// fp32 logits, loss / accuracy only (local_loss_function / accuracy_function on the logits Transformer.call returns,
+// transformer_model.py:11-26): same online max / sum and first-max argmax as above, nothing rounded to bf16, no gradient.
+__global__ void __launch_bounds__(kCeThreads)
+vocab_ce_f32_kernel(const float* __restrict__ logits, int ldl, const long long* __restrict__ labels, int V,
+                    float* __restrict__ row_loss, int* __restrict__ row_correct) {
+  __shared__ float sm_m[kCeThreads / 32], sm_s[kCeThreads / 32], sm_am[kCeThreads / 32];
+  __shared__ int sm_ai[kCeThreads / 32];
+  const int row = blockIdx.x;
+  const float* x = logits + size_t(row) * ldl;
+  const long long label = labels[row];
+  if (label == 0) {
+    if (threadIdx.x == 0) { row_loss[row] = 0.f; row_correct[row] = 0; }
+    return;
+  }
+  MaxSum ms{-INFINITY, 0.f};
+  float am = -INFINITY; int ai = 0x7fffffff;
+  for (int i = threadIdx.x; i < V; i += kCeThreads) {
+    const float f = x[i];
+    if (f > am) { am = f; ai = i; ms.s *= fast_exp2((ms.m - f) * kLog2eCe); ms.m = f; }
+    ms.s += fast_exp2((f - ms.m) * kLog2eCe);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    MaxSum other{__shfl_xor_sync(0xffffffffu, ms.m, o), __shfl_xor_sync(0xffffffffu, ms.s, o)};
+    ms = combine(ms, other);
+    const float om = __shfl_xor_sync(0xffffffffu, am, o); const int oi = __shfl_xor_sync(0xffffffffu, ai, o);
+    if (om > am || (om == am && oi < ai)) { am = om; ai = oi; }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) { sm_m[warp] = ms.m; sm_s[warp] = ms.s; sm_am[warp] = am; sm_ai[warp] = ai; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    MaxSum t{sm_m[0], sm_s[0]}; float bm = sm_am[0]; int bi = sm_ai[0];
+    for (int w = 1; w < kCeThreads / 32; ++w) {
+      t = combine(t, MaxSum{sm_m[w], sm_s[w]});
+      if (sm_am[w] > bm || (sm_am[w] == bm && sm_ai[w] < bi)) { bm = sm_am[w]; bi = sm_ai[w]; }
+    }
+    const float xl = (label > 0 && label < V) ? x[label] : 0.f;
+    row_loss[row] = t.m + logf(t.s) - xl;
+    row_correct[row] = (bi == int(label)) ? 1 : 0;
+  }
+}
+
 __global__ void ce_finalize_kernel(const float* __restrict__ row_loss, const int* __restrict__ row_correct,
                                    const int* __restrict__ nonpad_count, int rows, float inv_workers, float* __restrict__ out3) {
   pdl_wait();
@@ -652,6 +695,14 @@ int vocab_ce_fwd_bwd(bf16* logits, int ldl, const long long* labels, int rows, i
   if (ldl % 8) return set_error("vocab_ce: ld=%d must be a multiple of 8", ldl);
   if (rows <= 0) return 0;
   B200XF_CUDA(launch_k(vocab_ce_kernel, rows, kCeThreads, 0, stream, logits, ldl, labels, V, nonpad_count, inv_workers, row_loss, row_correct, write_grad));
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+int vocab_ce_f32(const float* logits, int ldl, const long long* labels, int rows, int V, float* row_loss, int* row_correct, cudaStream_t stream) {
+  if (rows <= 0) return 0;
+  vocab_ce_f32_kernel<<<rows, kCeThreads, 0, stream>>>(logits, ldl, labels, V, row_loss, row_correct);
   B200XF_CUDA(cudaGetLastError());
   count_launch();
   return 0;

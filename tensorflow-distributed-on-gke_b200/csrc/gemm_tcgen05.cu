@@ -33,19 +33,25 @@ constexpr int BM = 128;
 constexpr int BK = 64;       // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
 constexpr int kThreads = 320;  // warp0 TMA, warp1 MMA, warps 2-9 epilogue (two per TMEM lane quarter, half the columns each)
+// Weight-gradient layout (A and B both MN-major): two more warps (10, 11) that sum the columns of the B tiles in shared memory
+// while the tensor core consumes them -- the bias gradient of the same Dense, for free (GemmArgs::colsum_partials).
+constexpr int kThreadsWgrad = 384;
 
 // PAIR: two CTAs of a cluster (the two SMs of a TPC) work on one 256 x BN tile with cta_group::2 MMAs.  Each CTA stages
 // its own 128 rows of A and only HALF of the B tile (BN/2 columns; the tensor core reads the other half from the peer),
 // so a k-block costs each SM 16 KB + BN*64 B of L2 -> shared-memory traffic instead of 16 KB + BN*128 B: the K=512 GEMMs
 // of the model, which run at the per-SM L2 bandwidth, get a third of it back.
-template <int BN, bool PAIR>
+template <int BN, bool PAIR, bool LNF = false>
 struct Cfg {
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = (PAIR ? BN / 2 : BN) * BK * 2;  // per CTA
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (192 * 1024 / kStageBytes) > 8 ? 8 : (192 * 1024 / kStageBytes);  // 48 KB: 4, 32 KB: 6, 24 KB: 8
-  static constexpr int kSmem = kStages * kStageBytes + 4 * 2 * 4096 /*store staging*/ + 1024 /*bias slice*/ + 1024 /*align slack*/ + 256 /*barriers*/;
-  static constexpr int kTmemCols = 2 * BN;  // double-buffered accumulator
+  static constexpr int kStagesFull = (192 * 1024 / kStageBytes) > 8 ? 8 : (192 * 1024 / kStageBytes);  // 48 KB: 4, 32 KB: 6, 24 KB: 8
+  // the fused-LayerNorm variant keeps gamma / beta slices and the per-row statistics in shared memory as well
+  static constexpr int kStages = !LNF ? kStagesFull : (BN == 256 ? 3 : (kStagesFull > 5 ? 5 : kStagesFull));
+  static constexpr int kLnBytes = LNF ? (2 * 256 * 4 + 8 * 2 * BM * 8) : 0;  // gamma, beta slices; {local mean, M2} per source CTA, column half and row
+  static constexpr int kSmem = kStages * kStageBytes + 4 * 2 * 4096 /*store staging*/ + 1024 /*bias slice*/ + kLnBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kTmemCols = LNF ? BN : 2 * BN;  // double-buffered accumulator (one tile per CTA with the fused LayerNorm)
 };
 
 struct GemmParams {
@@ -58,6 +64,9 @@ struct GemmParams {
   unsigned long long* trace;  // debug: 8 globaltimer stamps per CTA (null in production)
   DropArgs drop;
   int b_static;  // B is not written by the kernel launched just before this one: its first tiles may be fetched before griddepcontrol.wait
+  float* colsum;  // weight-gradient layout: [splits][N] partial column sums of B (null: off)
+  // fused LayerNorm (LNF instantiations)
+  const float* ln_gamma; const float* ln_beta; float* ln_mean; float* ln_rstd; float ln_eps;
 };
 
 // bias add, ReLU, residual add / ReLU mask on 32 accumulator columns [col0, col0+32) of one output row.
@@ -113,11 +122,31 @@ __device__ __forceinline__ void stamp(const GemmParams& p, int slot) {
   }
 }
 
-template <int BN, int A_MN, int B_MN, bool PAIR>
-__global__ void __launch_bounds__(kThreads, 1)
+// Reads of another CTA's shared memory within the thread-block cluster (distributed shared memory).
+__device__ __forceinline__ float2 ld_cluster_f2(const void* local_smem_ptr, uint32_t cta_rank) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(ptx::smem_u32(local_smem_ptr)), "r"(cta_rank));
+  float2 v;
+  asm volatile("ld.shared::cluster.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(remote) : "memory");
+  return v;
+}
+
+// Store into the shared memory of CTA `cta_rank` of the cluster, at the offset the pointer has in this CTA's.
+__device__ __forceinline__ void st_cluster_f2(void* local_smem_ptr, uint32_t cta_rank, float2 v) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(ptx::smem_u32(local_smem_ptr)), "r"(cta_rank));
+  asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(remote), "f"(v.x), "f"(v.y) : "memory");
+}
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+
+template <int BN, int A_MN, int B_MN, bool PAIR, bool LNF>
+__global__ void __launch_bounds__((A_MN && B_MN) ? kThreadsWgrad : kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-            const __grid_constant__ CUtensorMap tmap_d, const GemmParams p) {
-  using C = Cfg<BN, PAIR>;
+            const __grid_constant__ CUtensorMap tmap_d, const __grid_constant__ CUtensorMap tmap_y, const GemmParams p) {
+  using C = Cfg<BN, PAIR, LNF>;
+  static_assert(!(LNF && PAIR), "the fused LayerNorm uses its cluster for the row statistics");
+  constexpr bool WGRAD = A_MN && B_MN;
   constexpr int BNC = PAIR ? BN / 2 : BN;  // B columns this CTA stages
   const int rank = PAIR ? int(ptx::cluster_ctarank()) : 0;   // 0 = the pair's leader: arms the barriers' byte counts, issues the MMAs
   const int worker = PAIR ? int(blockIdx.x >> 1) : int(blockIdx.x), workers = PAIR ? int(gridDim.x >> 1) : int(gridDim.x);
@@ -127,14 +156,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* stage_base = smem + C::kStages * C::kStageBytes;  // 8 epilogue warps x 4 KB store staging
   float* sbias = reinterpret_cast<float*>(stage_base + 8 * 4096);  // [256] bias slice of the current tile
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sbias + 256);
+  float* sgamma = sbias + 256;                                      // LNF: [256] gamma, [256] beta, [2][BM] {mean, M2}
+  float* sbeta = sgamma + 256;
+  float2* sstat = reinterpret_cast<float2*>(sbeta + 256);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sbias + 256) + C::kLnBytes);
   uint64_t* empty_bar = full_bar + C::kStages;
   uint64_t* tmem_full = empty_bar + C::kStages;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  // CTA pairs: the loads of BOTH CTAs are credited to the leader's full barrier, so the second CTA has no local signal that a
+  // stage has landed; when its column-sum warps need one, the leader's MMA thread forwards it to the peer's full2 barrier.
+  uint64_t* full2_bar = tmem_empty + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(full2_bar + C::kStages);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const bool colsum_on = WGRAD && p.colsum != nullptr;
   if (threadIdx.x == 0) {
     stamp(p, 0);
     if (p.trace && blockIdx.x == 0)  // slot 7 of CTA 0 identifies the launch: M, N, K and the operand majors
@@ -146,7 +182,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     ptx::prefetch_tmap(&tmap_a);
     ptx::prefetch_tmap(&tmap_b);
     if (p.d_tma) ptx::prefetch_tmap(&tmap_d);
-    for (int i = 0; i < C::kStages; ++i) { ptx::mbar_init(&full_bar[i], 1); ptx::mbar_init(&empty_bar[i], 1); }
+    if (LNF) ptx::prefetch_tmap(&tmap_y);
+    // a stage is free again once its MMAs have retired and, when the column sums are on, both summing warps have read it
+    for (int i = 0; i < C::kStages; ++i) { ptx::mbar_init(&full_bar[i], 1); ptx::mbar_init(&empty_bar[i], colsum_on ? 3 : 1); ptx::mbar_init(&full2_bar[i], 1); }
     // tmem_empty collects the epilogue warps of BOTH CTAs of a pair (the leader's MMA thread is the only waiter)
     for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tmem_full[i], 1); ptx::mbar_init(&tmem_empty[i], PAIR ? 16 : 8); }
     ptx::fence_barrier_init();
@@ -161,6 +199,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   const uint32_t tmem_base = *tmem_slot;
   const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
   const int total_kb = (p.K + BK - 1) / BK;
+  // Tile order.  Default: consecutive CTAs walk down the rows of one column tile (they share the B tile in L2).  With the
+  // fused LayerNorm the CTAs of a cluster hold the column tiles of ONE row block: tn = rank in the cluster.
+  auto tile_tm = [&](int t) { return LNF ? t / p.tiles_n : t % p.tiles_m; };
+  auto tile_tn = [&](int t) { return LNF ? t % p.tiles_n : (t / p.tiles_m) % p.tiles_n; };
   // This CTA's share of a k-block: its 128 rows of A, and its BNC columns of B (all of them, or its half of a pair's).
   auto load_a = [&](uint8_t* sa, uint64_t* bar, int tm, int kb) {
     const int row0 = (PAIR ? tm * 2 + rank : tm) * BM;
@@ -193,7 +235,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   int prefetched = 0;
   if (p.b_static && threadIdx.x == 0 && worker < total_tiles) {
     const int t = worker;
-    const int tn = (t / p.tiles_m) % p.tiles_n, z = t / (p.tiles_m * p.tiles_n);
+    const int tn = tile_tn(t), z = t / (p.tiles_m * p.tiles_n);
     const int kb0 = z * p.kb_per_split;
     const int kb1 = min(total_kb, kb0 + p.kb_per_split);
     prefetched = min(C::kStages, kb1 - kb0);
@@ -207,12 +249,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   pdl_trigger();
   if (threadIdx.x == 0) stamp(p, 1);
 
+  // LNF: what the epilogue threads carry from their first pass (z, packed bf16) into the second (y = LayerNorm(z))
+  constexpr int kChunksPerHalf = (BN / 32) / 2;
+  // tiles of >= 128 columns: the two warps of a lane quarter take half of the columns each; narrower: the first takes all
+  constexpr bool kLnSplit = kChunksPerHalf >= 2;
+  constexpr int kLnChunks = LNF ? (kLnSplit ? kChunksPerHalf : BN / 32) : 1;
+  uint32_t zp[kLnChunks][16];
+  (void)zp;
+
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (one lane)
     if (lane == 0) {
       int s = 0; uint32_t ph = 0;
       for (int t = worker; t < total_tiles; t += workers) {
-        const int tm = t % p.tiles_m, tn = (t / p.tiles_m) % p.tiles_n, z = t / (p.tiles_m * p.tiles_n);
+        const int tm = tile_tm(t), tn = tile_tn(t), z = t / (p.tiles_m * p.tiles_n);
         const int kb0 = z * p.kb_per_split;
         const int kb1 = min(total_kb, kb0 + p.kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -241,13 +291,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         const int z = t / (p.tiles_m * p.tiles_n);
         const int kb0 = z * p.kb_per_split;
         const int kb1 = min(total_kb, kb0 + p.kb_per_split);
-        const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
+        const int as = LNF ? 0 : (it & 1); const uint32_t aph = LNF ? 0 : ((it >> 1) & 1);
         ptx::mbar_wait(&tmem_empty[as], aph ^ 1);
         ptx::tc_fence_after();
         const uint32_t tmem_d = tmem_base + as * BN;
         for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(&full_bar[s], ph);
           ptx::tc_fence_after();
+          if (PAIR && WGRAD && colsum_on) ptx::mbar_arrive_peer_release(&full2_bar[s], 1);
           if (it == 0 && kb == kb0) stamp(p, 2);
           const uint32_t sa = ptx::smem_u32(smem + s * C::kStageBytes);
           const uint32_t sb = sa + C::kABytes;
@@ -267,25 +318,79 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         if (it == 0) stamp(p, 3);
       }
     }
+  } else if (WGRAD && warp >= 10) {
+    // ------------------------------------------------------------ column sums of B (the bias gradient), two warps
+    // B tile of a stage: BNC / 64 chunks of [64 k rows][64 columns] bf16, rows 128 B apart, 16-byte units XOR-swizzled by
+    // (k & 7).  A warp owns every second chunk; lane l owns columns 2l, 2l+1 of it: 32 consecutive words of a row per
+    // access, conflict-free.
+    if (colsum_on) {
+      constexpr int kMyChunks = (BNC / 64 + 1) / 2;
+      const int w = warp - 10;
+      int s = 0; uint32_t ph = 0;
+      for (int t = worker; t < total_tiles; t += workers) {
+        const int tm = tile_tm(t), tn = tile_tn(t), z = t / (p.tiles_m * p.tiles_n);
+        const int kb0 = z * p.kb_per_split;
+        const int kb1 = min(total_kb, kb0 + p.kb_per_split);
+        // The CTAs of the tiles_m row blocks of one column tile all stream the same B; each sums every tiles_m-th k-block, so
+        // the extra shared-memory reads (which compete with the tensor core's operand reads) are spread evenly.
+        float acc[kMyChunks][2];
+#pragma unroll
+        for (int c = 0; c < kMyChunks; ++c) acc[c][0] = acc[c][1] = 0.f;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          if (PAIR && rank == 1) ptx::mbar_wait_cluster(&full2_bar[s], ph); else ptx::mbar_wait(&full_bar[s], ph);
+          if ((kb - kb0) % p.tiles_m == tm) {
+            const uint8_t* sb = smem + s * C::kStageBytes + C::kABytes;
+#pragma unroll
+            for (int c = 0; c < kMyChunks; ++c) {
+              const int chunk = c * 2 + w;
+              if (chunk < BNC / 64) {
+                const uint8_t* base = sb + chunk * 8192 + ((lane & 3) << 2);
+#pragma unroll 16
+                for (int k = 0; k < 64; ++k) {
+                  const uint32_t v = *reinterpret_cast<const uint32_t*>(base + k * 128 + ((((lane >> 2) ^ (k & 7))) << 4));
+                  acc[c][0] += ptx::bf16_lo(v); acc[c][1] += ptx::bf16_hi(v);
+                }
+              }
+            }
+          }
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&empty_bar[s]);
+          if (++s == C::kStages) { s = 0; ph ^= 1; }
+        }
+#pragma unroll
+        for (int c = 0; c < kMyChunks; ++c) {
+          const int chunk = c * 2 + w;
+          const int col = tn * BN + rank * BNC + chunk * 64 + 2 * lane;
+          if (chunk < BNC / 64 && col < p.N) {
+            float* dst = p.colsum + (size_t(z) * p.tiles_m + tm) * p.N + col;   // one partial row per (K split, row block)
+            dst[0] = acc[c][0];
+            if (col + 1 < p.N) dst[1] = acc[c][1];
+          }
+        }
+      }
+    }
   } else {
-    // ------------------------------------------------------------ epilogue (4 warps, 128 TMEM lanes)
+    // ------------------------------------------------------------ epilogue (8 warps, 128 TMEM lanes)
     const int quarter = warp & 3;  // TMEM lane quarter this warp may touch
     constexpr int kBiasPerThread = 1;  // 256 epilogue threads cover BN <= 256 columns
     // this warp's share of the tile's 32-column chunks: the two warps of a lane quarter split the columns
     const int halfsel = (warp - 2) >> 2;
-    constexpr int kChunksPerHalf = (BN / 32) / 2;
     float bias_pre[kBiasPerThread];
 #pragma unroll
     for (int k = 0; k < kBiasPerThread; ++k) {  // first tile's bias slice
       const int j = int(threadIdx.x) - 64 + k * 256;
-      const int tn0 = (worker / p.tiles_m) % p.tiles_n;
+      const int tn0 = tile_tn(worker);
       bias_pre[k] = (p.bias != nullptr && worker < total_tiles && j < BN && tn0 * BN + j < p.N) ? __ldg(p.bias + tn0 * BN + j) : 0.f;
+      if (LNF) {  // gamma / beta slices of this CTA's columns
+        const bool ok = j < BN && tn0 * BN + j < p.N;
+        if (j < 256) { sgamma[j] = ok ? __ldg(p.ln_gamma + tn0 * BN + j) : 0.f; sbeta[j] = ok ? __ldg(p.ln_beta + tn0 * BN + j) : 0.f; }
+      }
     }
     int it = 0;
     for (int t = worker; t < total_tiles; t += workers, ++it) {
-      const int tn = (t / p.tiles_m) % p.tiles_n, z = t / (p.tiles_m * p.tiles_n);
-      const int tm = PAIR ? (t % p.tiles_m) * 2 + rank : t % p.tiles_m;  // this CTA's 128-row block
-      const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
+      const int tn = tile_tn(t), z = t / (p.tiles_m * p.tiles_n);
+      const int tm = PAIR ? tile_tm(t) * 2 + rank : tile_tm(t);  // this CTA's 128-row block
+      const int as = LNF ? 0 : (it & 1); const uint32_t aph = LNF ? 0 : ((it >> 1) & 1);
       const int row = tm * BM + quarter * 32 + lane;
       const bool row_ok = row < p.M;
       // the residual of this thread's first 64 columns is requested before the accumulator is ready, so that its L2
@@ -314,14 +419,113 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         asm volatile("bar.sync 1, 256;" ::: "memory");
       }
       if (p.bias != nullptr && t + workers < total_tiles) {  // fetch the next tile's slice now; it is needed a whole tile later
-        const int tn_next = ((t + workers) / p.tiles_m) % p.tiles_n;
+        const int tn_next = tile_tn(t + workers);
 #pragma unroll
         for (int k = 0; k < kBiasPerThread; ++k) {
           const int j = int(threadIdx.x) - 64 + k * 256;
           bias_pre[k] = (j < BN && tn_next * BN + j < p.N) ? __ldg(p.bias + tn_next * BN + j) : 0.f;
         }
       }
-      if (p.d_tma) {
+      if constexpr (LNF) {
+        // ---- fused LayerNorm, pass 1: z = epilogue(acc), rounded to bf16 (what the backward pass and the statistics see),
+        // stored through the staging tile, kept packed in registers; per-thread {mean, M2} of its columns.
+        uint8_t* buf = stage_base + (warp - 2) * 4096;
+        const int c_begin = kLnSplit ? halfsel * kChunksPerHalf : 0;
+        const bool active = kLnSplit || halfsel == 0;
+        float lsum = 0.f, lsq = 0.f, pivot = 0.f; int cnt = 0;
+        const bool full_tile = (tn + 1) * BN <= p.N;   // CTA-uniform: no column of this tile lies past N
+        if (active) {
+#pragma unroll
+          for (int cc = 0; cc < kLnChunks; ++cc) {
+            const int col0 = tn * BN + (c_begin + cc) * 32;
+            uint32_t v[32];
+            ptx::tmem_ld_32x32(taddr + (c_begin + cc) * 32, v);
+            ptx::tmem_ld_wait();
+            float f[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
+            if (col0 < p.N) epilogue_math(f, p, row, row_ok, col0, add_bias ? sbias + (c_begin + cc) * 32 : nullptr,
+                                          (rpre_ok && cc < 2) ? rpre + cc * 4 : nullptr);
+            if (full_tile) {
+              // one pass: sums of (x - pivot) and (x - pivot)^2 with the thread's first value as pivot (no cancellation beyond
+              // the spread of the row segment itself)
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const uint32_t w2 = ptx::pack_bf16x2(f[2 * j], f[2 * j + 1]);
+                zp[cc][j] = w2;
+                if (cc == 0 && j == 0) pivot = ptx::bf16_lo(w2);
+                const float a = ptx::bf16_lo(w2) - pivot, b = ptx::bf16_hi(w2) - pivot;
+                lsum += a + b;
+                lsq = fmaf(a, a, lsq); lsq = fmaf(b, b, lsq);
+              }
+              cnt += 32;
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const bool ok0 = col0 + 2 * j < p.N, ok1 = col0 + 2 * j + 1 < p.N;
+                const uint32_t w2 = ptx::pack_bf16x2(ok0 ? f[2 * j] : 0.f, ok1 ? f[2 * j + 1] : 0.f);
+                zp[cc][j] = w2;
+                lsum += ptx::bf16_lo(w2) + ptx::bf16_hi(w2);
+                cnt += int(ok0) + int(ok1);
+              }
+            }
+          }
+        }
+        float lmean, m2 = 0.f;
+        if (full_tile) {
+          const float dm = cnt > 0 ? lsum / float(cnt) : 0.f;   // mean of (x - pivot)
+          lmean = pivot + dm;
+          m2 = fmaxf(lsq - lsum * dm, 0.f);                     // sum (x - mean)^2 = sum d^2 - (sum d)^2 / n
+        } else {
+          lmean = cnt > 0 ? lsum / float(cnt) : 0.f;
+          if (active) {
+#pragma unroll
+            for (int cc = 0; cc < kLnChunks; ++cc) {
+              const int col0 = tn * BN + (c_begin + cc) * 32;
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const float a = ptx::bf16_lo(zp[cc][j]) - lmean, b = ptx::bf16_hi(zp[cc][j]) - lmean;
+                if (col0 + 2 * j < p.N) m2 += a * a;
+                if (col0 + 2 * j + 1 < p.N) m2 += b * b;
+              }
+            }
+          }
+        }
+        // every CTA of the cluster receives this thread's {mean, M2} in the slot of the sending CTA: after the one cluster
+        // barrier below each CTA reads only its own shared memory, and nobody touches a peer's again (no exit hazard)
+        {
+          const uint32_t my_rank = uint32_t(tn);
+          float2* slot = &sstat[(my_rank * 2 + halfsel) * BM + quarter * 32 + lane];
+          for (int r = 0; r < p.tiles_n; ++r) st_cluster_f2(slot, uint32_t(r), make_float2(lmean, m2));
+        }
+        cluster_arrive();
+        // z out: two 32-column chunks per 128-byte staging row and TMA box
+        if (active) {
+#pragma unroll 1
+          for (int c0 = 0; c0 < kLnChunks; c0 += 2) {
+            const int colbase = tn * BN + (c_begin + c0) * 32;
+            if (colbase >= p.N) break;
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            __syncwarp();
+#pragma unroll
+            for (int cc = 0; cc < 2; ++cc) {
+              if (c0 + cc < kLnChunks) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                  *reinterpret_cast<uint4*>(buf + lane * 128 + (((cc * 4 + q) ^ (lane & 7)) << 4)) =
+                      make_uint4(zp[c0 + cc][q * 4], zp[c0 + cc][q * 4 + 1], zp[c0 + cc][q * 4 + 2], zp[c0 + cc][q * 4 + 3]);
+              }
+            }
+            ptx::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              ptx::tma_store_2d(&tmap_d, buf, colbase, tm * BM + quarter * 32);
+              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+          }
+        }
+        ptx::tc_fence_before();
+      } else if (p.d_tma) {
         // TMEM -> registers -> 128B-swizzled staging tile (32 rows x 128 B, one per warp) -> TMA store /
         // TMA reduce-add: coalesced, asynchronous, clipped to the tensor bounds by the hardware.
         const int chunks = p.d_fp32 ? 1 : 2;      // fp32: 32 columns = 128 B per row; bf16 packs two 32-column chunks per box
@@ -413,13 +617,97 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         }
       }
       }
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) { if (PAIR) ptx::mbar_arrive_leader(&tmem_empty[as]); else ptx::mbar_arrive(&tmem_empty[as]); }
+      if constexpr (!LNF) {
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) { if (PAIR) ptx::mbar_arrive_leader(&tmem_empty[as]); else ptx::mbar_arrive(&tmem_empty[as]); }
+      }
       if (it == 0 && warp == 2 && lane == 0) stamp(p, 5);
     }
     // the staging buffers must outlive the stores' reads of them; the writes themselves complete with the grid
-    if (p.d_tma && lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    if (!LNF && p.d_tma && lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+  }
+
+  if constexpr (LNF) {
+    // ---- fused LayerNorm, pass 2.  Every CTA of the cluster has parked its threads' {mean, M2}; combine the 2 x cluster-size
+    // parts of each row (Chan's parallel variance: exact two-pass results per part, merged), normalise the register-held
+    // z and store y.  The cluster barriers involve every thread of every CTA (the producer / MMA warps just pass through).
+    if (warp < 2) cluster_arrive();   // the epilogue warps arrived right after publishing their statistics
+    cluster_wait();
+    if (threadIdx.x == 64 && blockIdx.x != 0) stamp(p, 7);  // (slot 7 of CTA 0 identifies the launch)
+    if (warp >= 2 && warp < 10 && worker < total_tiles) {
+      const int quarter = warp & 3, halfsel = (warp - 2) >> 2;
+      const int t = worker;
+      const int tm = tile_tm(t), tn = tile_tn(t);
+      const int row = tm * BM + quarter * 32 + lane;
+      const bool active = kLnSplit || halfsel == 0;
+      constexpr int kHalfCols = kLnChunks * 32;
+      constexpr int kParts = kLnSplit ? 2 : 1;
+      const int csize = p.tiles_n;
+      float mean = 0.f;
+      float2 st[16];
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+          st[r * 2 + h] = (r < csize && h < kParts) ? sstat[(r * 2 + h) * BM + quarter * 32 + lane] : make_float2(0.f, 0.f);
+      auto part_cnt = [&](int r, int h) { return max(0, min(kHalfCols, p.N - (r * BN + h * kHalfCols))); };
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+          if (r < csize && h < kParts) mean += st[r * 2 + h].x * float(part_cnt(r, h));
+      mean /= float(p.N);
+      float m2 = 0.f;
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+          if (r < csize && h < kParts) { const float dlt = st[r * 2 + h].x - mean; m2 += st[r * 2 + h].y + float(part_cnt(r, h)) * dlt * dlt; }
+      const float rstd = 1.0f / sqrtf(m2 / float(p.N) + p.ln_eps);  // biased variance, as tf.nn.moments
+      if (tn == 0 && halfsel == 0 && row < p.M) { p.ln_mean[row] = mean; p.ln_rstd[row] = rstd; }
+      if (active) {
+        uint8_t* buf = stage_base + (warp - 2) * 4096;
+        const int c_begin = kLnSplit ? halfsel * kChunksPerHalf : 0;
+#pragma unroll 1
+        for (int c0 = 0; c0 < kLnChunks; c0 += 2) {
+          const int colbase = tn * BN + (c_begin + c0) * 32;
+          if (colbase >= p.N) break;
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          __syncwarp();
+#pragma unroll
+          for (int cc = 0; cc < 2; ++cc) {
+            if (c0 + cc < kLnChunks) {
+              const float* g = sgamma + (c_begin + c0 + cc) * 32;
+              const float* b = sbeta + (c_begin + c0 + cc) * 32;
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                uint32_t o[4];
+                const float4 g0 = *reinterpret_cast<const float4*>(g + q * 8), g1 = *reinterpret_cast<const float4*>(g + q * 8 + 4);
+                const float4 b0 = *reinterpret_cast<const float4*>(b + q * 8), b1 = *reinterpret_cast<const float4*>(b + q * 8 + 4);
+                const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const int j = q * 4 + e;
+                  const float y0 = fmaf((ptx::bf16_lo(zp[c0 + cc][j]) - mean) * rstd, gg[2 * e], bb[2 * e]);
+                  const float y1 = fmaf((ptx::bf16_hi(zp[c0 + cc][j]) - mean) * rstd, gg[2 * e + 1], bb[2 * e + 1]);
+                  o[e] = ptx::pack_bf16x2(y0, y1);
+                }
+                *reinterpret_cast<uint4*>(buf + lane * 128 + (((cc * 4 + q) ^ (lane & 7)) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
+              }
+            }
+          }
+          ptx::fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            ptx::tma_store_2d(&tmap_y, buf, colbase, tm * BM + quarter * 32);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+        }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      }
+    }
   }
 
   ptx::tc_fence_before();
@@ -484,11 +772,12 @@ int get_tmap(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint3
   return 0;
 }
 
-template <int BN, int A_MN, int B_MN, bool PAIR>
-int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const GemmParams& p, int grid, cudaStream_t stream) {
-  auto kern = gemm_kernel<BN, A_MN, B_MN, PAIR>;
-  B200XF_TRY(ensure_dynamic_smem(kern, Cfg<BN, PAIR>::kSmem));
-  cudaError_t e = launch_k_cluster(kern, grid, kThreads, Cfg<BN, PAIR>::kSmem, stream, PAIR ? 2 : 1, ta, tb, td, p);
+template <int BN, int A_MN, int B_MN, bool PAIR, bool LNF = false>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const CUtensorMap& ty, const GemmParams& p, int grid,
+           int cluster, cudaStream_t stream) {
+  auto kern = gemm_kernel<BN, A_MN, B_MN, PAIR, LNF>;
+  B200XF_TRY(ensure_dynamic_smem(kern, Cfg<BN, PAIR, LNF>::kSmem));
+  cudaError_t e = launch_k_cluster(kern, grid, (A_MN && B_MN) ? kThreadsWgrad : kThreads, Cfg<BN, PAIR, LNF>::kSmem, stream, cluster, ta, tb, td, ty, p);
   if (e != cudaSuccess) return set_error("gemm launch: %s", cudaGetErrorString(e));
   count_launch();
   return 0;
@@ -496,11 +785,23 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, 
 
 template <int BN, bool PAIR>
 int launch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const GemmParams& p, int grid, cudaStream_t s) {
-  if (!a_mn && b_mn) return launch<BN, 0, 1, PAIR>(ta, tb, td, p, grid, s);
-  if (!a_mn && !b_mn) return launch<BN, 0, 0, PAIR>(ta, tb, td, p, grid, s);
-  if (a_mn && b_mn) return launch<BN, 1, 1, PAIR>(ta, tb, td, p, grid, s);
-  return launch<BN, 1, 0, PAIR>(ta, tb, td, p, grid, s);
+  const int cl = PAIR ? 2 : 1;
+  if (!a_mn && b_mn) return launch<BN, 0, 1, PAIR>(ta, tb, td, td, p, grid, cl, s);
+  if (!a_mn && !b_mn) return launch<BN, 0, 0, PAIR>(ta, tb, td, td, p, grid, cl, s);
+  if (a_mn && b_mn) return launch<BN, 1, 1, PAIR>(ta, tb, td, td, p, grid, cl, s);
+  return launch<BN, 1, 0, PAIR>(ta, tb, td, td, p, grid, cl, s);
 }
+
+// fused LayerNorm: forward (B MN-major) and data-gradient (B K-major) layouts, A K-major
+template <int BN>
+int launch_lnf(int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const CUtensorMap& ty, const GemmParams& p, int grid,
+               int cluster, cudaStream_t s) {
+  if (b_mn) return launch<BN, 0, 1, false, true>(ta, tb, td, ty, p, grid, cluster, s);
+  return launch<BN, 0, 0, false, true>(ta, tb, td, ty, p, grid, cluster, s);
+}
+
+// tile width of the fused-LayerNorm variant: the row block's column tiles must fit one cluster (<= 8 CTAs)
+int lnf_bn(int N) { return N <= 64 ? 64 : ((N + 127) / 128 <= 8 ? 128 : 256); }
 
 std::atomic<int> g_pair_mode{-2};
 int pair_mode() {  // 0 never, 1 whenever the problem has at least two 128-row blocks, -1 heuristic (B200XF_GEMM_PAIR sets the default)
@@ -511,9 +812,22 @@ int pair_mode() {  // 0 never, 1 whenever the problem has at least two 128-row b
 
 }  // namespace
 
-int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
+bool gemm_ln_fusable(int M, int N) { return M > 0 && N > 0 && N % 8 == 0 && (N + lnf_bn(N) - 1) / lnf_bn(N) <= 8; }
+
+static int gemm_impl(const GemmArgs& a, cudaStream_t stream, GemmInfo* info, bool plan_only);
+int gemm_bf16(const GemmArgs& a, cudaStream_t stream, GemmInfo* info) { return gemm_impl(a, stream, info, false); }
+int gemm_plan(const GemmArgs& a, GemmInfo* info) { return gemm_impl(a, nullptr, info, true); }
+
+static int gemm_impl(const GemmArgs& a, cudaStream_t stream, GemmInfo* info, bool plan_only) {
   if (a.M <= 0 || a.N <= 0 || a.K <= 0) return set_error("gemm: empty problem M=%d N=%d K=%d", a.M, a.N, a.K);
   if (a.accumulate && !a.d_fp32) return set_error("gemm: accumulate requires fp32 output");
+  const bool lnf = a.ln_y != nullptr;
+  if (lnf) {
+    if (a.d_fp32 || a.accumulate || a.a_mn || !a.ln_gamma || !a.ln_beta || !a.ln_mean || !a.ln_rstd)
+      return set_error("gemm: the fused LayerNorm needs a bf16, non-accumulating, K-major-A problem with gamma / beta / mean / rstd");
+    if (!gemm_ln_fusable(a.M, a.N)) return set_error("gemm: width %d cannot carry the fused LayerNorm", a.N);
+  }
+  if (a.colsum_partials && !(a.a_mn && a.b_mn)) return set_error("gemm: column sums of B are produced in the weight-gradient layout only");
   const int nsm = (a.max_ctas > 0 && a.max_ctas < num_sms()) ? a.max_ctas : num_sms();  // SMs this launch may fill
   const int tiles_m = (a.M + BM - 1) / BM;
   const int total_kb = (a.K + BK - 1) / BK;
@@ -533,7 +847,7 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
     const long waves = (ctas + nsm - 1) / nsm;
     return waves * (long(kb_per) * (cand + 64) + 4L * cand);
   };
-  int bn = a.force_bn, splits = 1;
+  int bn = lnf ? lnf_bn(a.N) : a.force_bn, splits = 1;
   if (bn == 0) {
     long best = -1;
     for (int cand : {256, 128, 64}) {
@@ -550,12 +864,12 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   // cluster scheduling plus the pair's extra synchronisation are fixed costs: 4.08 ms/step with them, 4.02 without), and
   // single-wave problems lose 10-20%; 128-wide pair tiles always lose.  Hence: at least three waves of 256-wide tiles.
   const long wide_tiles = long(tiles_m) * ((a.N + 255) / 256);
-  const bool pair_auto = a.N > 256 && wide_tiles >= 3L * nsm;
-  if (a.force_bn == 0 && a.pair >= 0 && pair_mode() < 0 && pair_auto && a.M > BM && nsm >= 2) bn = 256;
+  const bool pair_auto = !lnf && a.N > 256 && wide_tiles >= 3L * nsm;
+  if (!lnf && a.force_bn == 0 && a.pair >= 0 && pair_mode() < 0 && pair_auto && a.M > BM && nsm >= 2) bn = 256;
   if (bn != 64 && bn != 128 && bn != 256) return set_error("gemm: unsupported BN %d", bn);
   const int tiles_n = (a.N + bn - 1) / bn;
   plan(bn, &splits);
-  const bool pair_ok = a.pair >= 0 && bn >= 128 && a.M > BM && nsm >= 2;
+  const bool pair_ok = !lnf && a.pair >= 0 && bn >= 128 && a.M > BM && nsm >= 2;
   const bool pair = pair_ok && (a.pair > 0 || pair_mode() == 1 || (pair_mode() < 0 && pair_auto && bn == 256));
   int tiles_m_eff = tiles_m;
   if (pair) {
@@ -582,9 +896,13 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   p.bias = a.bias; p.relu = a.relu;
   p.resid = reinterpret_cast<const __nv_bfloat16*>(a.resid); p.ldr = a.ldr; p.resid_op = a.resid ? a.resid_op : 0;
   p.alpha = a.alpha;
-  p.trace = g_gemm_trace ? g_gemm_trace + size_t(g_gemm_trace_next++ % g_gemm_trace_slots) * (148 * 8) : nullptr;
+  p.trace = (g_gemm_trace && !plan_only) ? g_gemm_trace + size_t(g_gemm_trace_next++ % g_gemm_trace_slots) * (148 * 8) : nullptr;
   p.drop = a.drop;
   p.b_static = a.b_static;
+  p.colsum = a.colsum_partials;
+  p.ln_gamma = a.ln_gamma; p.ln_beta = a.ln_beta; p.ln_mean = a.ln_mean; p.ln_rstd = a.ln_rstd; p.ln_eps = a.ln_eps;
+  if (info) { info->splits = splits; info->tiles_m = tiles_m_eff; info->tiles_n = tiles_n; info->bn = bn; info->pair = pair ? 1 : 0; info->fused_ln = lnf ? 1 : 0; }
+  if (plan_only) return 0;
 
   CUtensorMap ta, tb;
   int rc;
@@ -601,6 +919,18 @@ int gemm_bf16(const GemmArgs& a, cudaStream_t stream) {
   if (p.d_tma) { rc = get_tmap(a.d, a.N, a.M, a.ldd, 32, &td, a.d_fp32 ? 1 : 0); if (rc) return rc; }
 
   const int total = tiles_m_eff * tiles_n * splits;
+  if (lnf) {
+    if (!p.d_tma) return set_error("gemm: the fused LayerNorm stores through TMA (16-byte aligned rows)");
+    CUtensorMap ty;
+    rc = get_tmap(a.ln_y, a.N, a.M, a.ln_ldy, 32, &ty, 0);
+    if (rc) return rc;
+    const int grid = tiles_m * tiles_n;  // one tile per CTA; a cluster = the tiles_n column tiles of a row block
+    switch (bn) {
+      case 64: return launch_lnf<64>(a.b_mn, ta, tb, td, ty, p, grid, tiles_n, stream);
+      case 128: return launch_lnf<128>(a.b_mn, ta, tb, td, ty, p, grid, tiles_n, stream);
+      default: return launch_lnf<256>(a.b_mn, ta, tb, td, ty, p, grid, tiles_n, stream);
+    }
+  }
   if (pair) {
     const int grid = 2 * min(total, nsm / 2);
     if (bn == 128) return launch_major<128, true>(a.a_mn, a.b_mn, ta, tb, td, p, grid, stream);

@@ -88,8 +88,8 @@ struct GemmArgs {
   int pair = 0;          // CTA pairs (cta_group::2, 256-row tiles): 0 auto, 1 force when M >= 256, -1 never
   DropArgs drop;         // inverted dropout on (acc + bias) before the residual add (transformer_model.py:196,202,232,238,244)
   // Weight-gradient layout only (a_mn = b_mn = 1): also emit the column sums of B over the contraction dimension -- the bias
-  // gradient sum_tokens dY[token][n] of the Dense whose weight gradient this is -- as one partial row per K split:
-  // colsum_partials[z * N + n], z < GemmInfo::splits (summed later by reduce_partials).  B's tiles are already in shared memory.
+  // gradient sum_tokens dY[token][n] of the Dense whose weight gradient this is -- as GemmInfo::splits * GemmInfo::tiles_m
+  // partial rows of N floats (summed later by reduce_partials).  B's tiles are already in shared memory.
   float* colsum_partials = nullptr;
   // LayerNorm fused into the epilogue (N = the normalised width, bf16 output, no accumulate): d receives
   // z = epilogue(acc) (bias, dropout, residual add), ln_y receives (z - mean) * rstd * gamma + beta with the statistics taken
@@ -101,6 +101,7 @@ struct GemmArgs {
 struct GemmInfo { int splits = 1; int tiles_m = 0, tiles_n = 0; int bn = 0; int pair = 0; int fused_ln = 0; };
 bool gemm_ln_fusable(int M, int N);  // whether a GEMM of width N can carry the fused LayerNorm epilogue
 int gemm_bf16(const GemmArgs& a, cudaStream_t stream, GemmInfo* info = nullptr);
+int gemm_plan(const GemmArgs& a, GemmInfo* info);  // the tiling gemm_bf16 would choose (e.g. the number of K splits), nothing launched
 void gemm_clear_tensor_map_cache();
 void gemm_set_pair_mode(int mode);  // CTA pairs: -1 heuristic (default), 0 never, 1 whenever M > 128 and the tile is >= 128 wide
 // Cached 2-D TMA descriptor (128B swizzle) of a row-major matrix: kind 0 = bf16 with a 64-column box, 1 = fp32 with a
@@ -180,6 +181,8 @@ int prep_targets(const long long* target, long long* tgt_in, long long* labels, 
 // logits bf16 [rows, ldl]; writes dlogits in place; row_loss/row_correct fp32/int per row; finalize reduces them.
 int vocab_ce_fwd_bwd(bf16* logits, int ldl, const long long* labels, int rows, int V, const int* nonpad_count,
                      float inv_workers, float* row_loss, int* row_correct, int write_grad, cudaStream_t stream);
+// loss / accuracy terms from fp32 logits (no rounding, no gradient): the reference's public loss functions on Transformer.call's output
+int vocab_ce_f32(const float* logits, int ldl, const long long* labels, int rows, int V, float* row_loss, int* row_correct, cudaStream_t stream);
 int ce_finalize(const float* row_loss, const int* row_correct, const int* nonpad_count, int rows, float inv_workers,
                 float* out3 /* loss, acc_num, acc_den */, cudaStream_t stream);
 

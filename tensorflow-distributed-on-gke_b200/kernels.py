@@ -41,6 +41,34 @@ def gemm(a, b, *, a_mn=False, b_mn=False, bias=None, relu=False, resid=None, res
     return out
 
 
+def dense_layernorm_fwd(x, w, bias, resid, gamma, beta, eps=1e-6):
+    """z = resid + x @ w + bias (bf16), y = LayerNorm(z): one GEMM with the normalisation in its epilogue.
+    x [rows, d_in] bf16, w [d_in, d_out] bf16; returns (z, y, mean, rstd)."""
+    _need_cuda(x, w, gamma, beta)
+    rows, d_in = x.shape
+    d_out = w.shape[1]
+    z = torch.empty((rows, d_out), device=x.device, dtype=torch.bfloat16); y = torch.empty_like(z)
+    mean = torch.empty(rows, device=x.device, dtype=torch.float32); rstd = torch.empty_like(mean)
+    check(_lib.load().b200xf_dense_layernorm_fwd(ptr(x), x.stride(0), ptr(w), w.stride(0), ptr(bias), ptr(resid),
+                                                 resid.stride(0) if resid is not None else 0, ptr(z), z.stride(0), ptr(gamma), ptr(beta),
+                                                 ptr(y), y.stride(0), ptr(mean), ptr(rstd), rows, d_out, d_in, float(eps), stream_ptr()))
+    return z, y, mean, rstd
+
+
+def dense_wgrad_bias(x, dy, dw=None):
+    """dw += x^T dy (fp32), dbias = column sums of dy, from one pass over dy.  x [tokens, d_in], dy [tokens, d_out] bf16."""
+    _need_cuda(x, dy)
+    tokens, d_in = x.shape
+    d_out = dy.shape[1]
+    if dw is None:
+        dw = torch.zeros((d_in, d_out), device=x.device, dtype=torch.float32)
+    dbias = torch.empty(d_out, device=x.device, dtype=torch.float32)
+    scratch = torch.empty(148 * d_out, device=x.device, dtype=torch.float32)
+    check(_lib.load().b200xf_dense_wgrad_bias(ptr(x), x.stride(0), ptr(dy), dy.stride(0), ptr(dw), dw.stride(0), ptr(dbias), ptr(scratch),
+                                              scratch.numel(), tokens, d_in, d_out, stream_ptr()))
+    return dw, dbias
+
+
 def attention_fwd(q, k, v, key_tokens, causal, H):
     """q [B,Sq,H*dk], k/v [B,Sk,H*dk] bf16 (may be column slices of wider buffers); returns (o, lse)."""
     _need_cuda(q, k, v, key_tokens)

@@ -207,3 +207,11 @@ def make_test_step(transformer, test_loss=None, test_accuracy=None):
         if test_accuracy is not None: test_accuracy.update_state(res.accuracy)
         return res
     return test_step
+
+
+def make_distributed_test_step(strategy, test_step):
+    """`distributed_test_step` (__main__.py:134-137): strategy.run(test_step) on this replica's shard; like the reference it
+    returns nothing — the metrics objects given to make_test_step carry the result."""
+    def distributed_test_step(input, target):
+        strategy.run(test_step, args=(input, target))
+    return distributed_test_step

@@ -441,17 +441,20 @@ def build_model(transformer):
 
 # ------------------------------------------------------------------ loss / accuracy (transformer_model.py:7-26)
 def _ce_stats(actual, predicted, workers_count):
-    from .kernels import vocab_ce_fwd_bwd
+    """[loss, accuracy numerator, denominator] from fp32 logits, in fp32 (the reference computes both functions from the
+    fp32 logits of Transformer.call; nothing is rounded to bf16 here)."""
     predicted = torch.as_tensor(predicted)
     if not predicted.is_cuda:
         raise _lib.B200XFError("local_loss_function/accuracy_function need device logits: there is no CPU fallback")
-    actual = _cuda_tokens(actual, predicted.device)
+    actual = _cuda_tokens(actual, predicted.device).reshape(-1)
     V = predicted.shape[-1]
-    ld = (V + 7) // 8 * 8
     rows = actual.numel()
-    buf = torch.zeros((rows, ld), device=predicted.device, dtype=torch.bfloat16)
-    buf[:, :V] = predicted.reshape(rows, V).to(torch.bfloat16)
-    return vocab_ce_fwd_bwd(buf, actual.reshape(-1), V, workers_count, write_grad=False)
+    logits = predicted.reshape(rows, V).to(torch.float32).contiguous()
+    out = torch.empty(3, device=predicted.device, dtype=torch.float32)
+    scratch = torch.empty(2 * rows + 64, device=predicted.device, dtype=torch.float32)
+    with torch.cuda.device(predicted.device):
+        check(_lib.load().b200xf_vocab_ce_f32(ptr(logits), V, ptr(actual), rows, V, int(workers_count), ptr(out), ptr(scratch), _lib.stream_ptr()))
+    return out
 
 
 def local_loss_function(actual, predicted, workers_count):

@@ -307,3 +307,50 @@ def test_adam_tf_form(iterations):
     upd, upd_e = (w - w0).cpu().numpy(), we - w0.cpu().numpy()
     np.testing.assert_allclose(w.cpu().numpy(), we, rtol=0, atol=2e-6 * float(np.abs(upd_e).max() + 1e-30) + 2.4e-7 * float(w0.abs().max()))
     assert torch.equal(shadow, w.to(torch.bfloat16))
+
+
+# ------------------------------------------------------------------------------------------ fused GEMM epilogues (round 2)
+@pytest.mark.parametrize("rows,d_in,d_out", [(4096, 512, 512), (4096, 2048, 512), (300, 128, 128), (77, 64, 64), (512, 1024, 1024),
+                                              (130, 96, 200), (256, 256, 1536), (200, 64, 40)])
+@pytest.mark.parametrize("with_resid", [True, False])
+def test_dense_layernorm_fwd_fused(rows, d_in, d_out, with_resid):
+    """z = resid + x W + b and y = LayerNorm(z) from ONE GEMM (cluster of up to 8 CTAs exchanging row statistics) against
+    torch fp32: z bit-equal to the bf16 rounding of the fp32 expression up to accumulation order, y / mean / rstd with the
+    tolerances of test_layernorm_fwd_bwd."""
+    g = torch.Generator(device=DEV).manual_seed(rows + d_out)
+    x = _bf(torch.randn(rows, d_in, device=DEV, generator=g)); w = _bf(torch.randn(d_in, d_out, device=DEV, generator=g) / math.sqrt(d_in))
+    bias = torch.randn(d_out, device=DEV, generator=g); gamma = torch.randn(d_out, device=DEV, generator=g); beta = torch.randn(d_out, device=DEV, generator=g)
+    resid = _bf(torch.randn(rows, d_out, device=DEV, generator=g)) if with_resid else None
+    z, y, mean, rstd = K.dense_layernorm_fwd(x, w, bias, resid, gamma, beta, 1e-6)
+    torch.cuda.synchronize()
+    zr = x.float() @ w.float() + bias + (resid.float() if with_resid else 0.0)
+    assert _rel(z, zr) < 4e-3 and float((z.float() - zr).abs().max()) < 6e-2          # one bf16 rounding
+    zf = z.float()                                                                     # the statistics are those of the STORED z
+    ref = torch.nn.functional.layer_norm(zf, (d_out,), gamma, beta, 1e-6)
+    assert _rel(y, ref) < 4e-3 and float((y.float() - ref).abs().max()) < 6e-2
+    np.testing.assert_allclose(mean.cpu(), zf.mean(-1).cpu(), atol=2e-5, rtol=1e-5)
+    np.testing.assert_allclose(rstd.cpu(), (1.0 / torch.sqrt(zf.var(-1, unbiased=False) + 1e-6)).cpu(), rtol=2e-5)
+    # and against the two-kernel path (GEMM, then the LayerNorm kernel) on the same inputs
+    z2 = K.gemm(x, w, b_mn=True, bias=bias, resid=resid)
+    y2, _, mean2, rstd2 = K.layernorm_residual_fwd(z2, None, gamma, beta, 1e-6)
+    assert torch.equal(z2, z)
+    assert _rel(y, y2) < 1e-3
+    np.testing.assert_allclose(mean.cpu(), mean2.cpu(), atol=2e-6, rtol=1e-5)
+
+
+@pytest.mark.parametrize("tokens,d_in,d_out", [(4096, 512, 1536), (4096, 512, 512), (4096, 512, 2048), (2560, 128, 384), (300, 64, 200),
+                                               (4096, 512, 32000), (77, 40, 72)])
+def test_dense_wgrad_with_fused_bias_gradient(tokens, d_in, d_out):
+    """dW += x^T dy and dbias = sum_tokens dy from one weight-gradient GEMM (two extra warps sum the staged dy tiles; CTA
+    pairs for the vocabulary-sized case) against torch fp32."""
+    g = torch.Generator(device=DEV).manual_seed(tokens + d_out)
+    ld = (d_out + 7) // 8 * 8
+    x = _bf(torch.randn(tokens, d_in, device=DEV, generator=g))
+    dy = _bf(torch.randn(tokens, ld, device=DEV, generator=g))[:, :d_out]
+    dw0 = torch.randn(d_in, ld, device=DEV, generator=g)[:, :d_out]
+    dw = dw0.clone()
+    ldw = torch.zeros(d_in, ld, device=DEV); dwv = ldw[:, :d_out]; dwv.copy_(dw0)
+    _, dbias = K.dense_wgrad_bias(x, dy, dwv)
+    torch.cuda.synchronize()
+    assert _rel(dwv, dw0 + x.float().t() @ dy.float()) < 2e-5
+    assert _rel(dbias, dy.float().sum(0)) < 1e-5                                      # fp32 sums of exact bf16 values
