@@ -140,13 +140,14 @@ __device__ __forceinline__ void st_cluster_f2(void* local_smem_ptr, uint32_t cta
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 
-template <int BN, int A_MN, int B_MN, bool PAIR, bool LNF>
-__global__ void __launch_bounds__((A_MN && B_MN) ? kThreadsWgrad : kThreads, 1)
+template <int BN, int A_MN, int B_MN, bool PAIR, bool LNF, bool CS>
+__global__ void __launch_bounds__(CS ? kThreadsWgrad : kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
             const __grid_constant__ CUtensorMap tmap_d, const __grid_constant__ CUtensorMap tmap_y, const GemmParams p) {
   using C = Cfg<BN, PAIR, LNF>;
   static_assert(!(LNF && PAIR), "the fused LayerNorm uses its cluster for the row statistics");
-  constexpr bool WGRAD = A_MN && B_MN;
+  static_assert(!CS || (A_MN && B_MN), "column sums of B: weight-gradient layout only");
+  constexpr bool WGRAD = CS;   // the instantiations with the two column-sum warps
   constexpr int BNC = PAIR ? BN / 2 : BN;  // B columns this CTA stages
   const int rank = PAIR ? int(ptx::cluster_ctarank()) : 0;   // 0 = the pair's leader: arms the barriers' byte counts, issues the MMAs
   const int worker = PAIR ? int(blockIdx.x >> 1) : int(blockIdx.x), workers = PAIR ? int(gridDim.x >> 1) : int(gridDim.x);
@@ -184,7 +185,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     if (p.d_tma) ptx::prefetch_tmap(&tmap_d);
     if (LNF) ptx::prefetch_tmap(&tmap_y);
     // a stage is free again once its MMAs have retired and, when the column sums are on, both summing warps have read it
-    for (int i = 0; i < C::kStages; ++i) { ptx::mbar_init(&full_bar[i], 1); ptx::mbar_init(&empty_bar[i], colsum_on ? 3 : 1); ptx::mbar_init(&full2_bar[i], 1); }
+    for (int i = 0; i < C::kStages; ++i) {
+      ptx::mbar_init(&full_bar[i], 1); ptx::mbar_init(&empty_bar[i], colsum_on ? 3 : 1);
+      if (CS && PAIR) ptx::mbar_init(&full2_bar[i], 1);
+    }
     // tmem_empty collects the epilogue warps of BOTH CTAs of a pair (the leader's MMA thread is the only waiter)
     for (int i = 0; i < 2; ++i) { ptx::mbar_init(&tmem_full[i], 1); ptx::mbar_init(&tmem_empty[i], PAIR ? 16 : 8); }
     ptx::fence_barrier_init();
@@ -772,12 +776,12 @@ int get_tmap(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint3
   return 0;
 }
 
-template <int BN, int A_MN, int B_MN, bool PAIR, bool LNF = false>
+template <int BN, int A_MN, int B_MN, bool PAIR, bool LNF = false, bool CS = false>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& td, const CUtensorMap& ty, const GemmParams& p, int grid,
            int cluster, cudaStream_t stream) {
-  auto kern = gemm_kernel<BN, A_MN, B_MN, PAIR, LNF>;
+  auto kern = gemm_kernel<BN, A_MN, B_MN, PAIR, LNF, CS>;
   B200XF_TRY(ensure_dynamic_smem(kern, Cfg<BN, PAIR, LNF>::kSmem));
-  cudaError_t e = launch_k_cluster(kern, grid, (A_MN && B_MN) ? kThreadsWgrad : kThreads, Cfg<BN, PAIR, LNF>::kSmem, stream, cluster, ta, tb, td, ty, p);
+  cudaError_t e = launch_k_cluster(kern, grid, CS ? kThreadsWgrad : kThreads, Cfg<BN, PAIR, LNF>::kSmem, stream, cluster, ta, tb, td, ty, p);
   if (e != cudaSuccess) return set_error("gemm launch: %s", cudaGetErrorString(e));
   count_launch();
   return 0;
@@ -788,7 +792,7 @@ int launch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& t
   const int cl = PAIR ? 2 : 1;
   if (!a_mn && b_mn) return launch<BN, 0, 1, PAIR>(ta, tb, td, td, p, grid, cl, s);
   if (!a_mn && !b_mn) return launch<BN, 0, 0, PAIR>(ta, tb, td, td, p, grid, cl, s);
-  if (a_mn && b_mn) return launch<BN, 1, 1, PAIR>(ta, tb, td, td, p, grid, cl, s);
+  if (a_mn && b_mn) return p.colsum ? launch<BN, 1, 1, PAIR, false, true>(ta, tb, td, td, p, grid, cl, s) : launch<BN, 1, 1, PAIR>(ta, tb, td, td, p, grid, cl, s);
   return launch<BN, 1, 0, PAIR>(ta, tb, td, td, p, grid, cl, s);
 }
 
