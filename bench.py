@@ -413,7 +413,7 @@ def parity_block(model, name, cfg, hp, host_batch, world, rank, dist):
     return out
 
 
-def allreduce_block(model, hp, B, S, T, world, rank, dist, ms_per_step, n_params, dev_batches, steps):
+def allreduce_block(model, hp, B, S, T, world, rank, dist, ms_per_step, n_params, dev_batches, steps, solo_fits=True):
     """What the gradient exchange costs (N > 1): bytes, NCCL bus bandwidth on the library's communicator at the bucket
     sizes, and the step with and without collectives (a second, communicator-less model on the same GPU)."""
     import torch
@@ -439,6 +439,9 @@ def allreduce_block(model, hp, B, S, T, world, rank, dist, ms_per_step, n_params
     out["nccl_allreduce_sweep"] = sweep
     out["busbw_gbs_at_32MB"] = next(x["busbw_gbs"] for x in sweep if abs(x["mbytes"] - 33.554432) < 1)
     out["busbw_frac_of_900"] = out["busbw_gbs_at_32MB"] / 900.0
+    out["busbw_if_spread_over_step_gbs"] = out["bus_bytes_per_step"] / (ms_per_step * 1e-3) / 1e9
+    if not solo_fits:   # the long configuration fills the device: no room for a second model
+        return out
     # the same steps without any collective
     solo = b200xf.Transformer(**hp, max_tokens=B * max(S, T + 1), seed=0)
     solo.trainable_variables; solo.iterations = 1
@@ -578,7 +581,7 @@ def main():
         parity = parity_block(model, args.config, cfg, hp, host[0], world, rank, dist if world > 1 else None)
     allreduce = None
     if world > 1 and not args.no_allreduce_probe:
-        allreduce = allreduce_block(model, hp, B, S, T, world, rank, dist, ms / Ksteps, n_params, dev, min(Ksteps, 30))
+        allreduce = allreduce_block(model, hp, B, S, T, world, rank, dist, ms / Ksteps, n_params, dev, min(Ksteps, 30), solo_fits=args.config != "long")
     if rank != 0:
         model.close()
         if world > 1: dist.destroy_process_group()

@@ -87,6 +87,15 @@ int b200xf_forward(b200xf_ctx* ctx, const int64_t* inp, const int64_t* tgt_in, i
  * [B,H,T,S], fp32 DEVICE buffer, for the batch of the most recent b200xf_forward (whose token buffers must still be
  * alive).  tester.py:51-52 is the caller in the reference. */
 int b200xf_attention_weights(b200xf_ctx* ctx, int decoder_layer, int block, float* out);
+/* Incremental greedy decoding for the loop of tester.py:27-42.  The reference re-runs encoder and decoder over the whole prefix
+ * for every generated token; here b200xf_decode_begin runs the encoder once (inp [B,S] int64 DEVICE, must stay alive) and
+ * projects the cross-attention K|V of every decoder layer, and each b200xf_decode_step runs the decoder for ONE new target
+ * position t (tokens_t [B] int64 DEVICE = the target tokens at position t, t = 0 being the start token), appending that
+ * position's self-attention K|V to per-layer caches of max_target_length positions.  Outputs (either may be NULL): logits_out
+ * fp32 [B, V] of position t — the row Transformer.call would return at [:, t, :] — and next_tokens [B] = their argmax
+ * (lowest index among equal maxima, tester.py:38).  Steps must be issued for t = 0, 1, 2, ... in order. */
+int b200xf_decode_begin(b200xf_ctx* ctx, const int64_t* inp, int B, int S, int max_target_length);
+int b200xf_decode_step(b200xf_ctx* ctx, const int64_t* tokens_t, int t, float* logits_out, int64_t* next_tokens);
 /* tf.argmax(x, axis=-1) over fp32 DEVICE rows (tester.py:38): out[r] = lowest index of the maximum of row r. */
 int b200xf_argmax_rows(const float* x, int ld, int rows, int cols, int64_t* out, void* stream);
 

@@ -53,6 +53,8 @@ SIGNATURES = {
     "b200xf_set_iterations": (_I, [_P, _L]),
     "b200xf_get_iterations": (_I, [_P, C.POINTER(_L)]),
     "b200xf_forward": (_I, [_P, _P, _P, _I, _I, _I, _I, _P]),
+    "b200xf_decode_begin": (_I, [_P, _P, _I, _I, _I]),
+    "b200xf_decode_step": (_I, [_P, _P, _I, _P, _P]),
     "b200xf_attention_weights": (_I, [_P, _I, _I, _P]),
     "b200xf_argmax_rows": (_I, [_P, _I, _I, _I, _P, _P]),
     "b200xf_train_step_device": (_I, [_P, _P, _P, _I, _I, _I, _I, _P]),

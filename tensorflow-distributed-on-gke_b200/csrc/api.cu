@@ -113,6 +113,14 @@ int b200xf_dropout_mask(b200xf_ctx* ctx, int site, int rows, int cols, float* ou
   if (!d.thresh) return set_error("dropout is disabled (rate 0)");
   B200XF_SCOPED(ctx, dropout_mask_fill(out, rows, cols, d, c.stream));
 }
+int b200xf_decode_begin(b200xf_ctx* ctx, const int64_t* inp, int B, int S, int max_target_length) {
+  if (!ctx || !inp) return set_error("null argument");
+  B200XF_SCOPED(ctx, ctx->c.decode_begin(reinterpret_cast<const long long*>(inp), B, S, max_target_length));
+}
+int b200xf_decode_step(b200xf_ctx* ctx, const int64_t* tokens_t, int t, float* logits_out, int64_t* next_tokens) {
+  if (!ctx || !tokens_t) return set_error("null argument");
+  B200XF_SCOPED(ctx, ctx->c.decode_step(reinterpret_cast<const long long*>(tokens_t), t, logits_out, reinterpret_cast<long long*>(next_tokens)));
+}
 int b200xf_attention_weights(b200xf_ctx* ctx, int decoder_layer, int block, float* out) {
   if (!ctx || !out) return set_error("null argument");
   B200XF_SCOPED(ctx, ctx->c.attention_weights(decoder_layer, block, out));

@@ -476,8 +476,8 @@ int launch_attn(Kern kern, size_t smem, dim3 grid, const KernelArgs& p, cudaStre
 
 int attention_fwd(const AttnArgs& a, cudaStream_t stream) {
   B200XF_TRY(check(a, false));
-  if (attention_tc_supported(a)) return attention_fwd_tc(a, stream);
-  if (attention_tc_fwd_multi_supported(a)) return attention_fwd_tc_multi(a, stream);
+  if (!a.generic && attention_tc_supported(a)) return attention_fwd_tc(a, stream);
+  if (!a.generic && attention_tc_fwd_multi_supported(a)) return attention_fwd_tc_multi(a, stream);
   const KernelArgs p = pack(a);
   const dim3 grid((a.Sq + kTile - 1) / kTile, a.H, a.B);
   switch (a.dk) {

@@ -597,14 +597,10 @@ int Context::check_shapes(int B, int S, int T) {
   return 0;
 }
 
-int Context::forward(const long long* inp, const long long* tgt_in, int B, int S, int T, float* logits_f32, bool training) {
-  B200XF_TRY(check_shapes(B, S, T));
-  dropout_on = training && hp.droput_rate > 0.f;
-  last_B = B; last_S = S; last_T = T; last_inp = inp; last_tgt = tgt_in;
+int Context::forward_encoder(const long long* inp, int B, int S) {
   const int L = hp.layers_count, d = hp.embedding_size, H = hp.heads_count, dk = d / H;
-  const int Ns = B * S, Nt = B * T;
+  const int Ns = B * S;
   const size_t cap = size_t(hp.max_tokens) * d;
-
   // ---- encoder (transformer_model.py:270-279)
   B200XF_TRY(embed_pe_fwd(inp, params + enc_emb, hp.input_vocabulary_size, pe_in, enc_x, B, S, d, stream, site_drop(0)));
   for (int l = 0; l < L; ++l) {
@@ -622,7 +618,17 @@ int Context::forward(const long long* inp, const long long* tgt_in, int B, int S
     B200XF_TRY(dense_ln_fwd(a.h, Ns, w.f2, a.z2, a.o1, 3 + 2 * l, w.ln2, out, st + 2 * Ns, st + 3 * Ns));  // z2 = o1 + drop(ffn(o1)); out = LN2(z2)
   }
   const bf16* enc_out = enc_x + size_t(L) * cap;
-  B200XF_TRY(dense_fwd(enc_out, Ns, kv_all, kv, 0, nullptr));  // K|V of every decoder layer's cross-attention
+  return dense_fwd(enc_out, Ns, kv_all, kv, 0, nullptr);  // K|V of every decoder layer's cross-attention
+}
+
+int Context::forward(const long long* inp, const long long* tgt_in, int B, int S, int T, float* logits_f32, bool training) {
+  B200XF_TRY(check_shapes(B, S, T));
+  dropout_on = training && hp.droput_rate > 0.f;
+  last_B = B; last_S = S; last_T = T; last_inp = inp; last_tgt = tgt_in;
+  const int L = hp.layers_count, d = hp.embedding_size, H = hp.heads_count, dk = d / H;
+  const int Nt = B * T;
+  const size_t cap = size_t(hp.max_tokens) * d;
+  B200XF_TRY(forward_encoder(inp, B, S));
 
   // ---- decoder (transformer_model.py:301-315)
   B200XF_TRY(embed_pe_fwd(tgt_in, params + dec_emb, hp.target_vocabulary_size, pe_tgt, dec_x, B, T, d, stream, site_drop(1)));
@@ -659,6 +665,77 @@ int Context::forward(const long long* inp, const long long* tgt_in, int B, int S
   } else {
     B200XF_TRY(dense_fwd(dec_out, Nt, final_layer, logits, 0, nullptr));
   }
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------ incremental decoding
+int Context::decode_begin(const long long* inp, int B, int S, int Tmax) {
+  B200XF_TRY(check_shapes(B, S, Tmax));
+  dropout_on = false;
+  B200XF_TRY(forward_encoder(inp, B, S));
+  // the decoded tokens so far, [B, Tmax], PAD (0) beyond the current position: the self-attention masks those keys out
+  B200XF_CUDA(cudaMemsetAsync(tok_tgt_in, 0, size_t(B) * Tmax * sizeof(long long), stream));
+  dec_B = B; dec_S = S; dec_Tmax = Tmax; dec_inp = inp;
+  last_B = 0;  // the activations of the last full forward pass are gone: attention_weights needs a new one
+  return 0;
+}
+
+namespace {
+__global__ void put_tokens_kernel(const long long* __restrict__ tok, long long* __restrict__ all, int B, int Tmax, int t) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < B) all[size_t(b) * Tmax + t] = tok[b];
+}
+}  // namespace
+
+// One decoder pass over position t of every sentence (transformer_model.py:301-315 restricted to the newest target
+// position): tokens_t [B] are the target tokens at position t; logits_f32 [B, V] / next_tokens [B] (argmax) are optional.
+int Context::decode_step(const long long* tokens_t, int t, float* logits_f32, long long* next_tokens) {
+  if (dec_B <= 0) return set_error("decode_step: call decode_begin first");
+  if (t < 0 || t >= dec_Tmax) return set_error("decode_step: position %d outside the cache of %d", t, dec_Tmax);
+  const int L = hp.layers_count, d = hp.embedding_size, H = hp.heads_count, dk = d / H;
+  const int B = dec_B, S = dec_S, Tmax = dec_Tmax;
+  dropout_on = false;
+  put_tokens_kernel<<<(B + 127) / 128, 128, 0, stream>>>(tokens_t, tok_tgt_in, B, Tmax, t);
+  B200XF_CUDA(cudaGetLastError());
+  count_launch();
+  bf16* x = dA;  // [B, d] working rows (the backward pass's scratch is free during inference)
+  bf16* y = dB;
+  B200XF_TRY(embed_pe_fwd(tokens_t, params + dec_emb, hp.target_vocabulary_size, pe_tgt + size_t(t) * d, x, B, 1, d, stream, DropArgs()));
+  for (int l = 0; l < L; ++l) {
+    const DecLayer& w = dec[l]; DecAct& a = da[l];
+    float* st = a.stats;
+    {  // Q|K|V of the new position into row t of each sentence's cache (rows of one sentence are Tmax * 3d apart)
+      GemmArgs g;
+      g.a = x; g.lda = d; g.b = shadow + w.qkv1.w; g.ldb = w.qkv1.ld; g.b_mn = 1;
+      g.d = a.qkv + size_t(t) * 3 * d; g.ldd = Tmax * 3 * d;
+      g.M = B; g.N = 3 * d; g.K = d; g.bias = params + w.qkv1.b; g.b_static = weights_static & 1;
+      B200XF_TRY(gemm_bf16(g, stream));
+    }
+    AttnArgs s1;
+    s1.q = a.qkv + size_t(t) * 3 * d; s1.ldq = Tmax * 3 * d; s1.k = a.qkv + d; s1.v = a.qkv + 2 * d; s1.ldk = s1.ldv = 3 * d;
+    s1.o = a.ctx1; s1.ldo = d; s1.lse = a.lse1; s1.key_tokens = tok_tgt_in; s1.causal = 0;  // every cached key is <= t; later ones are PAD
+    s1.B = B; s1.H = H; s1.Sq = 1; s1.Sk = Tmax; s1.dk = dk; s1.generic = 1;
+    B200XF_TRY(attention_fwd(s1, stream));
+    B200XF_TRY(dense_ln_fwd(a.ctx1, B, w.o1, a.z1, x, -1, w.ln1, a.o1, st, st + B));
+    B200XF_TRY(dense_fwd(a.o1, B, w.q2, a.q2, 0, nullptr));
+    AttnArgs c2;
+    c2.q = a.q2; c2.ldq = d; c2.k = kv + size_t(l) * 2 * d; c2.v = kv + size_t(l) * 2 * d + d; c2.ldk = c2.ldv = kv_all.ld;
+    c2.o = a.ctx2; c2.ldo = d; c2.lse = a.lse2; c2.key_tokens = dec_inp; c2.causal = 0;
+    c2.B = B; c2.H = H; c2.Sq = 1; c2.Sk = S; c2.dk = dk; c2.generic = 1;
+    B200XF_TRY(attention_fwd(c2, stream));
+    B200XF_TRY(dense_ln_fwd(a.ctx2, B, w.o2, a.z2, a.o1, -1, w.ln2, a.o2, st + 2 * B, st + 3 * B));
+    B200XF_TRY(dense_fwd(a.o2, B, w.f1, a.h, 1, nullptr));
+    B200XF_TRY(dense_ln_fwd(a.h, B, w.f2, a.z3, a.o2, -1, w.ln3, y, st + 4 * B, st + 5 * B));
+    std::swap(x, y);
+  }
+  float* lg = logits_f32 ? logits_f32 : reinterpret_cast<float*>(logits);  // the training logits buffer (bf16 [N, V]) holds B fp32 rows
+  if (!logits_f32 && size_t(B) * final_layer.N * 4 > size_t(hp.max_tokens) * vt_ld * 2) return set_error("decode_step: batch too large for the logits buffer");
+  GemmArgs g;
+  g.a = x; g.lda = d; g.b = shadow + final_layer.w; g.ldb = final_layer.ld; g.b_mn = 1;
+  g.d = lg; g.ldd = final_layer.N; g.d_fp32 = 1;
+  g.M = B; g.N = final_layer.N; g.K = d; g.bias = params + final_layer.b;
+  B200XF_TRY(gemm_bf16(g, stream));
+  if (next_tokens) B200XF_TRY(argmax_rows(lg, final_layer.N, B, final_layer.N, next_tokens, stream));
   return 0;
 }
 

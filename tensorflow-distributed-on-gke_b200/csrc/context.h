@@ -158,6 +158,12 @@ struct Context {
   int attention_weights(int layer, int block, float* out);
   int check_shapes(int B, int S, int T);
   int forward(const long long* inp, const long long* tgt_in, int B, int S, int T, float* logits_f32, bool training);
+  int forward_encoder(const long long* inp, int B, int S);   // encoder stack + the K|V projections of every decoder layer's cross-attention
+  // Incremental greedy decoding (tester.py:27-42 re-runs the whole model for every token; here the encoder output and the
+  // cross-attention K|V are computed once and each decoder layer keeps the K|V of the tokens decoded so far).
+  int dec_B = 0, dec_S = 0, dec_Tmax = 0; const long long* dec_inp = nullptr;
+  int decode_begin(const long long* inp, int B, int S, int Tmax);
+  int decode_step(const long long* tokens_t, int t, float* logits_f32, long long* next_tokens);
   int backward(const long long* inp, const long long* tgt_in, int B, int S, int T);
   int section_done();
   int loss_and_grad(int Nt, int workers_count, int write_grad);

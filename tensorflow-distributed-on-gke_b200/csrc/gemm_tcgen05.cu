@@ -122,15 +122,6 @@ __device__ __forceinline__ void stamp(const GemmParams& p, int slot) {
   }
 }
 
-// Reads of another CTA's shared memory within the thread-block cluster (distributed shared memory).
-__device__ __forceinline__ float2 ld_cluster_f2(const void* local_smem_ptr, uint32_t cta_rank) {
-  uint32_t remote;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(ptx::smem_u32(local_smem_ptr)), "r"(cta_rank));
-  float2 v;
-  asm volatile("ld.shared::cluster.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(remote) : "memory");
-  return v;
-}
-
 // Store into the shared memory of CTA `cta_rank` of the cluster, at the offset the pointer has in this CTA's.
 __device__ __forceinline__ void st_cluster_f2(void* local_smem_ptr, uint32_t cta_rank, float2 v) {
   uint32_t remote;

@@ -132,6 +132,7 @@ struct AttnArgs {
   // bit 0: q, bit 1: k and v are NOT outputs of the kernel launched just before this one on the stream (e.g. saved
   // forward activations in the backward pass): the single-tile tcgen05 kernels fetch them ahead of the dependency wait
   int early = 0;
+  int generic = 0;  // forward: take the general (mma.sync) kernel whatever the shape (incremental decoding: Sq = 1 with strided rows)
 };
 int attention_fwd(const AttnArgs& a, cudaStream_t stream);
 int attention_bwd(const AttnArgs& a, cudaStream_t stream);

@@ -409,11 +409,15 @@ class Transformer:
         self.save_weights(str(Path(path) / "variables" / "variables"))
 
 
-def greedy_decode(transformer, encoder_input, start_id, end_id, max_length=20):
-    """The decode loop of tester.py:13-53 without its tokenizers: starting from `start_id`, feed the growing target back
-    through the model (the reference re-encodes the source every step; so does this), append the argmax of the last
-    position, stop at `end_id` or after `max_length` tokens.  Returns (tokens [1, n] int64 on the device,
-    attention_weights of the final pass over output[:, :-1])."""
+def greedy_decode(transformer, encoder_input, start_id, end_id, max_length=20, use_cache=True):
+    """The decode loop of tester.py:13-53 without its tokenizers: starting from `start_id`, append the argmax of the last
+    position, stop at `end_id` or after `max_length` tokens.  Returns (tokens [1, n] int64 on the device, attention_weights
+    of the final pass over output[:, :-1]).
+
+    The reference re-runs encoder and decoder over the whole prefix for every token (tester.py:32); with use_cache=True
+    (default) the encoder output and the cross-attention K|V are computed once and every decoder layer keeps the K|V of the
+    tokens decoded so far (b200xf_decode_begin / b200xf_decode_step) — the same tokens, one decoder position per step.
+    use_cache=False is the reference's loop."""
     enc = _cuda_tokens(encoder_input, transformer.device)
     if enc.dim() == 1:
         enc = enc[None, :]
@@ -421,15 +425,55 @@ def greedy_decode(transformer, encoder_input, start_id, end_id, max_length=20):
     out = torch.full((1, 1), int(start_id), device=transformer.device, dtype=torch.int64)
     V = transformer.hparams["target_vocabulary_size"]
     nxt = torch.empty(1, device=transformer.device, dtype=torch.int64)
-    for _ in range(int(max_length)):
-        logits, _ = transformer([enc, out], training=False)
-        last = logits[0, -1]
-        check(_lib.load().b200xf_argmax_rows(ptr(last), V, 1, V, ptr(nxt), _lib.stream_ptr()))
-        out = torch.cat([out, nxt[None, :]], dim=1)
-        if int(nxt.item()) == int(end_id):
-            break
+    lib = _lib.load()
+    if use_cache:
+        S = enc.shape[1]
+        transformer._ensure_built(max(S, int(max_length) + 1))
+        transformer._sync_weights()
+        transformer._forward_serial += 1
+        check(lib.b200xf_decode_begin(transformer._ctx, ptr(enc), 1, S, int(max_length) + 1))
+        cur = out[:, 0].contiguous()
+        for t in range(int(max_length)):
+            check(lib.b200xf_decode_step(transformer._ctx, ptr(cur), t, None, ptr(nxt)))
+            out = torch.cat([out, nxt[None, :]], dim=1)
+            if int(nxt.item()) == int(end_id):
+                break
+            cur = nxt.clone()
+    else:
+        for _ in range(int(max_length)):
+            logits, _ = transformer([enc, out], training=False)
+            last = logits[0, -1]
+            check(lib.b200xf_argmax_rows(ptr(last), V, 1, V, ptr(nxt), _lib.stream_ptr()))
+            out = torch.cat([out, nxt[None, :]], dim=1)
+            if int(nxt.item()) == int(end_id):
+                break
     _, weights = transformer([enc, out[:, :-1]], training=False)
     return out, weights
+
+
+def greedy_decode_batch(transformer, encoder_input, start_id, end_id, max_length=20):
+    """Batched incremental greedy decoding over the K|V caches: every sentence of `encoder_input` [B, S] advances one
+    position per step; a sentence that has produced `end_id` keeps emitting PAD (0).  Returns tokens [B, n] (device)."""
+    enc = _cuda_tokens(encoder_input, transformer.device)
+    B, S = enc.shape
+    lib = _lib.load()
+    transformer._ensure_built(max(B * S, B * (int(max_length) + 1)))
+    transformer._sync_weights()
+    transformer._forward_serial += 1
+    check(lib.b200xf_decode_begin(transformer._ctx, ptr(enc), B, S, int(max_length) + 1))
+    cur = torch.full((B,), int(start_id), device=transformer.device, dtype=torch.int64)
+    done = torch.zeros(B, device=transformer.device, dtype=torch.bool)
+    cols = [cur.clone()]
+    nxt = torch.empty(B, device=transformer.device, dtype=torch.int64)
+    for t in range(int(max_length)):
+        check(lib.b200xf_decode_step(transformer._ctx, ptr(cur), t, None, ptr(nxt)))
+        tok = torch.where(done, torch.zeros_like(nxt), nxt)
+        cols.append(tok)
+        done = done | (tok == int(end_id))
+        if bool(done.all()):
+            break
+        cur = tok.clone()
+    return torch.stack(cols, dim=1)
 
 
 def build_model(transformer):
