@@ -83,7 +83,10 @@ if __name__ == "__main__":
                for e in e2 if e["dtype"] == 1]
     tensors.sort(key=lambda t: t["offset"])
     total = sum(t["size"] for t in tensors)
+    # the Keras object graph (DT_STRING scalar): both checkpoints record the same offset, size and masked CRC32C for it
+    og2 = [e for e in e2 if e["key"] == "_CHECKPOINTABLE_OBJECT_GRAPH"][0]; og1 = [e for e in e1 if e["key"] == "_CHECKPOINTABLE_OBJECT_GRAPH"][0]
+    assert og1 == og2
     OUT.write_text(json.dumps(dict(source=str(SRC), n_tensors=len(tensors), total_bytes=total,
-                                   total_params=total // 4, tensors=tensors), indent=1))
+                                   total_params=total // 4, object_graph=og2, tensors=tensors), indent=1))
     print(len(tensors), total, total // 4)
     for t in tensors[:30]: print(t)

@@ -49,11 +49,17 @@ def test_written_index_matches_the_reference_layout(tmp_path):
     arrays = O.init_parameters(4, 128, 512, 7765, 7010, seed=3)     # the tutorial model: 172 variables, 18 587 528 bytes
     ck.save_weights(_HostModel(arrays), tmp_path / "model_weights")
     got = {e["key"]: e for e in ck.read_index(str(tmp_path / "model_weights.index"))}
+    og = got.pop(ck.OBJECT_GRAPH_KEY)
+    # The Keras object graph that load_weights (__main__.py:87) restores by: the reference's own index records this entry's
+    # offset, size and masked CRC32C (its data shard is missing), and the rebuilt graph reproduces all three exactly.
+    assert {k: og[k] for k in ("dtype", "shape", "offset", "size", "crc32c")} == {k: GOLD["object_graph"][k] for k in ("dtype", "shape", "offset", "size", "crc32c")}
+    assert (og["size"], og["crc32c"]) == (22436, 1911686991)
     assert len(got) == 172
     for t in GOLD["tensors"]:                                        # offsets, sizes and shapes of the reference's own index
         e = got[t["name"] + ck.SUFFIX]
         assert (e["offset"], e["size"], e["shape"], e["dtype"]) == (t["offset"], t["size"], t["shape"], 1), t["name"]
-    assert (tmp_path / "model_weights.data-00000-of-00001").stat().st_size == GOLD["total_bytes"] == 18587528
+    assert GOLD["total_bytes"] == 18587528
+    assert (tmp_path / "model_weights.data-00000-of-00001").stat().st_size == GOLD["total_bytes"] + 22436   # tensors + object graph
     assert (tmp_path / "checkpoint").read_text() == 'model_checkpoint_path: "model_weights"\nall_model_checkpoint_paths: "model_weights"\n'
     back = ck.load_arrays(tmp_path / "model_weights")
     assert list(back) == sorted(arrays)                              # SSTable keys are sorted
@@ -88,3 +94,26 @@ def test_reader_decodes_the_reference_index_files():
             assert (e["offset"], e["size"], e["shape"]) == (t["offset"], t["size"], t["shape"])
         with pytest.raises(FileNotFoundError):                             # the data shards are not in the repository
             ck.load_arrays(REF / n / "model_weights")
+
+
+def test_object_graph_structure():
+    """The TrackableObjectGraph written under _CHECKPOINTABLE_OBJECT_GRAPH: every variable's checkpoint key appears exactly once
+    as an attribute, node ids are a breadth-first numbering, and the graph scales with the layer count."""
+    for L in (1, 4, 6):
+        proto = ck.object_graph_proto(L)
+        nodes = [ck._parse_proto(n) for n in ck._parse_proto(proto)[1]]
+        keys = []
+        for n in nodes:
+            for att in n.get(2, []):
+                f = ck._parse_proto(att)
+                assert f[1] == [b"VARIABLE_VALUE"] and 2 not in f       # name, no full_name (as the reference's TF wrote it)
+                keys.append(f[3][0].decode())
+        names = O.parameter_names(L)
+        assert sorted(keys) == sorted(n + ck.SUFFIX for n in names) and len(keys) == len(set(keys))
+        ids = [ck._parse_proto(c)[1][0] for n in nodes for c in n.get(1, [])]
+        assert set(ids) == set(range(1, len(nodes)))                      # every node but the root is somebody's child
+        # root: encoder, decoder, final_layer
+        assert [ck._parse_proto(c)[2][0] for c in nodes[0][1]] == [b"encoder", b"decoder", b"final_layer"]
+    assert len(ck.object_graph_proto(4)) == 22429
+    blob, crc = ck.string_tensor_bytes(ck.object_graph_proto(4))
+    assert len(blob) == 22436 and crc == 0x71f2074f                        # saved_weights/{1,2}/model_weights.index of the reference
