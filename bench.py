@@ -421,7 +421,9 @@ def allreduce_block(model, hp, B, S, T, world, rank, dist, ms_per_step, n_params
     from b200xf._lib import load, ptr, check
     lib = load()
     out = {"wire_dtype": "fp32", "grad_bytes_per_step": int(n_params * 4), "bus_bytes_per_step": n_params * 4 * 2.0 * (world - 1) / world,
-           "nvlink_peak_gbs_per_direction": 900.0, "collective": "reduce-scatter + all-gather per >= 32 MB bucket (sharded Adam between them), NCCL"}
+           "nvlink_peak_gbs_per_direction": 900.0,
+           "collective": ("fused NVLS kernel per >= 32 MB bucket: multimem.ld_reduce of the rank's shard + Adam + multimem.st of the new weights to every replica"
+                          if getattr(model, "_symmetric", None) is not None else "reduce-scatter + all-gather per >= 32 MB bucket (sharded Adam between them), NCCL")}
     sweep = []
     for mb in (8, 32, 128, 373):
         n = min(mb << 18, (n_params // (world * 64)) * world * 64)
@@ -437,6 +439,22 @@ def allreduce_block(model, hp, B, S, T, world, rank, dist, ms_per_step, n_params
         sweep.append({"mbytes": n * 4 / 1e6, "us": us, "algbw_gbs": n * 4 / (us * 1e-6) / 1e9, "busbw_gbs": n * 4 / (us * 1e-6) / 1e9 * 2 * (world - 1) / world})
         del buf
     out["nccl_allreduce_sweep"] = sweep
+    if getattr(model, "_symmetric", None) is not None:
+        nv = []
+        for mb in (32, 64):
+            n = (mb << 18) // (world * 64) * world * 64
+            for _ in range(3): check(lib.b200xf_debug_nvls_update(model._ctx, 0, n, 64, 0))
+            torch.cuda.synchronize(); dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(10): check(lib.b200xf_debug_nvls_update(model._ctx, 0, n, 64, 0))
+            e1.record(); torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1) / 10], device="cuda", dtype=torch.float64); dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            us = float(t.item()) * 1e3
+            # per link direction the fused kernel moves the bucket once (every replica's gradients out, everybody's new weights in) plus one shard
+            nv.append({"mbytes": n * 4 / 1e6, "us": us, "algbw_gbs": n * 4 / (us * 1e-6) / 1e9, "link_gbs_per_direction": n * 4 * (1 + 1.0 / world) / (us * 1e-6) / 1e9,
+                       "frac_of_900": n * 4 * (1 + 1.0 / world) / (us * 1e-6) / 1e9 / 900.0})
+        out["nvls_fused_update_sweep"] = nv
     out["busbw_gbs_at_32MB"] = next(x["busbw_gbs"] for x in sweep if abs(x["mbytes"] - 33.554432) < 1)
     out["busbw_frac_of_900"] = out["busbw_gbs_at_32MB"] / 900.0
     out["busbw_if_spread_over_step_gbs"] = out["bus_bytes_per_step"] / (ms_per_step * 1e-3) / 1e9

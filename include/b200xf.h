@@ -155,6 +155,23 @@ int b200xf_comm_destroy(b200xf_ctx* ctx);
  * Each replica draws its own dropout masks: the rank is part of the mask key (see b200xf_set_dropout_seed). */
 int b200xf_gather_optimizer_state(b200xf_ctx* ctx);
 int b200xf_optimizer_state_complete(b200xf_ctx* ctx);
+/* The same exchange as ONE kernel over NVLink / NVSwitch (nvls_update.cu): each rank reads the SUM of every replica's gradients
+ * of its shard with multimem.ld_reduce (the switch adds in flight), applies Adam, and writes the new weights into every
+ * replica's memory with multimem.st, inbound and outbound traffic overlapping; NCCL is then only used for the three loss /
+ * accuracy scalars.  It needs the flat fp32 weights and gradients in SYMMETRIC memory with a multicast mapping, which the host
+ * side allocates (torch.distributed._symmetric_memory in training.py):
+ *   b200xf_use_external_state  moves weights and gradients into caller-owned DEVICE buffers (256-byte aligned, param_total
+ *                              floats each; contents are carried over; b200xf_param_ptr / b200xf_grad_ptr change);
+ *   b200xf_nvls_attach         after b200xf_comm_init: the multicast addresses of those two buffers and, per rank, the address
+ *                              of a zeroed symmetric flag pad of >= 256 bytes as mapped into this process; world <= 8;
+ *   b200xf_nvls_error          non-zero once a replica failed to arrive at a cross-replica flag within ~10 s.
+ * No counterpart in the reference beyond cluster/cluster.py:66: the collective is implicit there. */
+int b200xf_use_external_state(b200xf_ctx* ctx, float* params, float* grads);
+int b200xf_nvls_attach(b200xf_ctx* ctx, void* grads_multicast, void* params_multicast, void* const* flag_pads, int rank, int world);
+int b200xf_nvls_error(b200xf_ctx* ctx);
+/* Debug / benchmark aid: one fused update of the flat range [begin, begin + count) (count a multiple of 64 * world) on `ctas`
+ * CTAs, optionally followed by the bf16 refresh / gradient clear; every replica must call it with the same arguments. */
+int b200xf_debug_nvls_update(b200xf_ctx* ctx, int64_t begin, int64_t count, int ctas, int refresh);
 /* All-reduce (SUM, fp32, in place) of `count` floats at DEVICE pointer on the context's comm stream. */
 int b200xf_allreduce_bucket(b200xf_ctx* ctx, float* device_ptr, int64_t count);
 

@@ -151,6 +151,30 @@ int b200xf_comm_init(b200xf_ctx* ctx, const void* id, int rank, int world) {
   return ctx->c.comm_init(id, rank, world);
 }
 int b200xf_comm_destroy(b200xf_ctx* ctx) { return ctx ? ctx->c.comm_destroy() : set_error("null ctx"); }
+int b200xf_use_external_state(b200xf_ctx* ctx, float* params, float* grads) {
+  if (!ctx) return set_error("null ctx");
+  return ctx->c.use_external_state(params, grads);
+}
+int b200xf_nvls_attach(b200xf_ctx* ctx, void* grads_multicast, void* params_multicast, void* const* flag_pads, int rank, int world) {
+  if (!ctx) return set_error("null ctx");
+  return ctx->c.nvls_attach(grads_multicast, params_multicast, flag_pads, rank, world);
+}
+int b200xf_debug_nvls_update(b200xf_ctx* ctx, int64_t begin, int64_t count, int ctas, int refresh) {
+  if (!ctx || !ctx->c.nvls_on) return set_error("debug_nvls_update: the NVLS update is not attached");
+  Context& c = ctx->c;
+  if (begin < 0 || count <= 0 || size_t(begin + count) > c.total_params || count % (int64_t(c.world) * 64) || begin % 64) return set_error("debug_nvls_update: bad range");
+  const size_t sh = size_t(count) / c.world, off = size_t(begin) + size_t(c.rank) * sh;
+  B200XF_TRY(c.enter());
+  B200XF_TRY(nvls_reduce_adam_broadcast(c.nvls, c.params, c.adam_m, c.adam_v, off, sh, c.iterations_dev, c.adam, c.nvls_words, c.nvls_words + 1, ctas, c.stream));
+  if (refresh) B200XF_TRY(refresh_shadow_zero_grad(c.params + begin, c.shadow + begin, c.grads + begin, size_t(count), c.stream));
+  return c.leave();
+}
+int b200xf_nvls_error(b200xf_ctx* ctx) {
+  if (!ctx || !ctx->c.nvls_on) return 0;
+  unsigned v = 0;
+  if (cudaMemcpy(&v, ctx->c.nvls.pad_local + kNvlsError, sizeof(v), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+  return int(v);
+}
 int b200xf_gather_optimizer_state(b200xf_ctx* ctx) {
   if (!ctx) return set_error("null ctx");
   B200XF_SCOPED(ctx, ctx->c.gather_optimizer_state());

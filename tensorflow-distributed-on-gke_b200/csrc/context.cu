@@ -336,6 +336,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   iterations_dev = reinterpret_cast<long long*>(small);
   nonpad_count = reinterpret_cast<int*>(small + 64);
   metrics = reinterpret_cast<float*>(small + 256);      // 3 local + 3 reduced
+  nvls_words = reinterpret_cast<unsigned*>(small + 512); // launch counter and CTA counter of the NVLS update kernels (arena is zeroed)
 
   {
     std::vector<float> pe(size_t(std::max(hp.maximum_input_length, hp.maximum_target_length)) * d);
@@ -366,6 +367,8 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   if (const char* e = getenv("B200XF_BUCKET_JOIN")) bucket_join = atoi(e) != 0;
   if (const char* e = getenv("B200XF_PIPELINED_UPDATE")) pipelined_update = atoi(e);  // 0 off, 1 every bucket, 2 the last two bucket closes
   if (const char* e = getenv("B200XF_COMM_SMS")) comm_sms = std::max(0, atoi(e));
+  if (const char* e = getenv("B200XF_NVLS_CTAS")) nvls_ctas = std::max(1, atoi(e));
+  if (const char* e = getenv("B200XF_NVLS_TAIL_CTAS")) nvls_tail_ctas = std::max(1, atoi(e));
   if (const char* e = getenv("B200XF_WEIGHT_PREFETCH")) weights_static = atoi(e);  // bit mask, see context.h
   if (const char* e = getenv("B200XF_BUCKET_MB")) { bucket_bytes = size_t(std::max(1, atoi(e))) << 20; bucket_bytes_set = true; }
   B200XF_CUDA(cudaEventCreateWithFlags(&ev_ready, cudaEventDisableTiming));
@@ -388,7 +391,8 @@ Context::~Context() {
   if (stream) { cudaStreamSynchronize(stream); cudaStreamDestroy(stream); }
   if (ev_user) cudaEventDestroy(ev_user);
   if (ev_own) cudaEventDestroy(ev_own);
-  cudaFree(params); cudaFree(grads); cudaFree(adam_m); cudaFree(adam_v); cudaFree(shadow); cudaFree(arena);
+  if (!external_state) { cudaFree(params); cudaFree(grads); }
+  cudaFree(adam_m); cudaFree(adam_v); cudaFree(shadow); cudaFree(arena);
   if (host_out) cudaFreeHost(host_out);
   if (comm_stream) cudaStreamDestroy(comm_stream);
   if (upd_stream) cudaStreamDestroy(upd_stream);
@@ -450,9 +454,42 @@ int Context::comm_destroy() {
   if (upd_stream) cudaStreamSynchronize(upd_stream);
   drop_graphs();  // captured steps hold collectives of the communicator that goes away
   if (api) api->CommDestroy(static_cast<ncclComm_t>(comm));
-  comm = nullptr; world = 1; rank = 0;
+  comm = nullptr; world = 1; rank = 0; nvls_on = false;
   return 0;
 }
+// Parameters and gradients move into buffers the caller allocated (symmetric memory with a multicast mapping, so that the
+// NVLS update kernels can reduce / broadcast them across replicas); contents are carried over, the old buffers are released.
+int Context::use_external_state(float* params_ext, float* grads_ext) {
+  if (!params_ext || !grads_ext) return set_error("use_external_state: null buffer");
+  if ((reinterpret_cast<uintptr_t>(params_ext) | reinterpret_cast<uintptr_t>(grads_ext)) & 255) return set_error("use_external_state: buffers must be 256-byte aligned");
+  B200XF_CUDA(cudaSetDevice(device));
+  drop_graphs();
+  B200XF_CUDA(cudaMemcpyAsync(params_ext, params, total_params * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  B200XF_CUDA(cudaMemcpyAsync(grads_ext, grads, total_params * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  B200XF_CUDA(cudaStreamSynchronize(stream));
+  if (!external_state) { cudaFree(params); cudaFree(grads); }
+  params = params_ext; grads = grads_ext; external_state = true;
+  gemm_clear_tensor_map_cache();
+  return 0;
+}
+
+int Context::nvls_attach(void* grads_mc, void* params_mc, void* const* pads, int rank_, int world_) {
+  if (!comm || rank_ != rank || world_ != world) return set_error("nvls_attach: attach the communicator first (same rank / world)");
+  if (!external_state) return set_error("nvls_attach: parameters and gradients must live in symmetric memory (use_external_state)");
+  if (world_ < 2 || world_ > kNvlsMaxWorld) return set_error("nvls_attach: world of %d unsupported (2..%d)", world_, kNvlsMaxWorld);
+  if (!grads_mc || !params_mc || !pads) return set_error("nvls_attach: null multicast mapping");
+  nvls = NvlsComm();
+  nvls.grads_mc = static_cast<float*>(grads_mc); nvls.params_mc = static_cast<float*>(params_mc);
+  for (int r = 0; r < world_; ++r) { if (!pads[r]) return set_error("nvls_attach: null flag pad"); nvls.pad_peer[r] = static_cast<unsigned*>(pads[r]); }
+  nvls.pad_local = nvls.pad_peer[rank_];
+  nvls.rank = rank_; nvls.world = world_;
+  B200XF_CUDA(cudaMemsetAsync(nvls_words, 0, 2 * sizeof(unsigned), stream));
+  B200XF_CUDA(cudaStreamSynchronize(stream));
+  drop_graphs();
+  nvls_on = true;
+  return 0;
+}
+
 int Context::allreduce(float* ptr, size_t count, cudaStream_t s) {
   if (!comm) return set_error("no communicator attached");
   NcclApi* api = nccl_api();
@@ -937,7 +974,15 @@ int Context::section_done() {
   B200XF_TRY(flush_reductions(comm_stream));
   const size_t n = end - bucket_begin;
   NcclApi* api = comm ? nccl_api() : nullptr;
-  if (sharded_active() && api->ReduceScatter && api->AllGather && n % (size_t(world) * 64) == 0) {
+  if (nvls_on && sharded_active() && world > 1 && n % (size_t(world) * 64) == 0) {
+    // One kernel reduces this rank's shard over all replicas through the NVSwitch, applies Adam and broadcasts the new weights
+    // (nvls_update.cu); a one-CTA kernel waits for the other replicas; the local bf16 refresh / gradient clear follows.
+    const size_t sh = n / world, off = bucket_begin + size_t(rank) * sh;
+    const bool trailing = idx + 2 >= sections.size();   // nothing (or little) of backward is left to disturb
+    B200XF_TRY(nvls_reduce_adam_broadcast(nvls, params, adam_m, adam_v, off, sh, iterations_dev, adam, nvls_words, nvls_words + 1,
+                                          trailing ? nvls_tail_ctas : nvls_ctas, comm_stream));
+    B200XF_TRY(refresh_shadow_zero_grad(params + bucket_begin, shadow + bucket_begin, grads + bucket_begin, n, comm_stream));
+  } else if (sharded_active() && api->ReduceScatter && api->AllGather && n % (size_t(world) * 64) == 0) {
     // all-reduce = reduce-scatter + all-gather: put the Adam update between the two halves, on this rank's 1/world
     // shard only (same bytes on the wire, 1/world of the optimizer's HBM traffic), then gather the updated fp32
     // weights and refresh the bf16 operand copy / clear the gradients of the whole bucket in one pass

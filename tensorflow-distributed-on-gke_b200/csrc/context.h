@@ -7,6 +7,7 @@
 
 #include "../../include/b200xf.h"
 #include "internal.h"
+#include "nvls.h"
 
 namespace b200xf {
 
@@ -121,6 +122,13 @@ struct Context {
   bool overlap_single = true;   // single GPU too: each bucket's Adam runs on the update stream under the rest of backward (B200XF_OVERLAP_UPDATE=0 disables)
 
   static size_t arena_bytes_for(const b200xf_hparams& hp, int vt_ld, size_t* red_capacity_out, size_t* emb_scratch_out);
+  // ---- NVLS update path (nvls_update.cu): parameters and gradients in caller-provided symmetric memory
+  bool external_state = false;           // params / grads were handed in (use_external_state): not ours to free
+  int use_external_state(float* params_ext, float* grads_ext);
+  NvlsComm nvls; bool nvls_on = false;
+  unsigned* nvls_words = nullptr;        // [0] launch counter of the update kernels, [1] CTA counter
+  int nvls_ctas = 16, nvls_tail_ctas = 64;  // CTAs of the update kernel under backward / for the buckets that close after it (B200XF_NVLS_CTAS, _TAIL_CTAS)
+  int nvls_attach(void* grads_mc, void* params_mc, void* const* pads, int rank_, int world_);
   ~Context();
   int init(const b200xf_hparams& h, int dev, cudaStream_t s);
   void build_layout();

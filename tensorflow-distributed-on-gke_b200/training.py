@@ -115,8 +115,53 @@ class B200Strategy:
                 uid[0] = bytes(buf.raw)
             dist.broadcast_object_list(uid, src=0)
             model.comm_init(uid[0], self.rank, self.world_size)
+            # The fused NVLS update moves ~(1 + 1/W) bucket sizes per link direction where reduce-scatter + all-gather over
+            # point-to-point links move 2 (W-1)/W: it wins from 4 replicas up (measured: profiles/r02_nvls_update.md) and
+            # loses at 2.  B200XF_NVLS=1 / 0 forces it on / off.
+            mode = os.environ.get("B200XF_NVLS", "auto")
+            if mode == "1" or (mode not in ("0", "1") and self.world_size >= 4):
+                self._attach_nvls(model)
         self._models.append(model)
         return model
+
+    def _attach_nvls(self, model):
+        """Move the model's flat weights and gradients into symmetric memory with a multicast (NVLS) mapping and switch the
+        gradient exchange to the fused multimem kernel (reduce-scatter + Adam + all-gather in one launch).  Falls back to the
+        NCCL path when the box offers no multicast mapping (B200XF_NVLS=0 forces that)."""
+        import ctypes as C
+        import torch.distributed as dist
+        if self.world_size > 8:
+            return False
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            lib = _lib.load()
+            total = int(lib.b200xf_param_total(model._ctx))
+            dev = model.device
+            group = dist.group.WORLD.group_name
+            bufs = [symm_mem.empty(total, dtype=torch.float32, device=dev) for _ in range(2)]
+            pad = symm_mem.empty(256, dtype=torch.int32, device=dev)
+            handles = [symm_mem.rendezvous(t, group) for t in bufs + [pad]]
+            ok = all(int(h.multicast_ptr) != 0 for h in handles[:2])
+        except Exception as e:  # no symmetric memory on this build / box
+            ok = False; why = repr(e)
+        flag = torch.tensor([1 if ok else 0], device=model.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)           # all replicas take the same path
+        if int(flag.item()) == 0:
+            if self.rank == 0 and os.environ.get("B200XF_NVLS") == "1":
+                print(f"[b200xf] NVLS update unavailable, using NCCL: {locals().get('why', 'no multicast mapping')}", flush=True)
+            return False
+        for t in bufs:
+            t.zero_()
+        pad.zero_()
+        check(lib.b200xf_use_external_state(model._ctx, C.c_void_p(bufs[0].data_ptr()), C.c_void_p(bufs[1].data_ptr())))
+        model._bind(model._ctx)                                  # the variable views now wrap the symmetric buffers
+        torch.cuda.synchronize(model.device)
+        dist.barrier()                                           # every replica's buffers and flag pad are initialised
+        pads = (C.c_void_p * self.world_size)(*[int(p) for p in handles[2].buffer_ptrs])
+        check(lib.b200xf_nvls_attach(model._ctx, C.c_void_p(int(handles[1].multicast_ptr)), C.c_void_p(int(handles[0].multicast_ptr)),
+                                     pads, self.rank, self.world_size))
+        model._symmetric = (bufs, pad, handles)                  # keep the allocations alive as long as the model
+        return True
 
     def run(self, fn, args=(), kwargs=None):
         return fn(*args, **(kwargs or {}))

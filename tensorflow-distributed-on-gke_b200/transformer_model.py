@@ -172,6 +172,7 @@ class Transformer:
         self._dirty = False
         self.variables = []
         self._comm = None
+        self._symmetric = None   # symmetric-memory allocations behind weights / gradients once the NVLS update is attached
         self._forward_serial = 0
 
     # ---- context management ---------------------------------------------------------------
@@ -260,6 +261,7 @@ class Transformer:
             self._flats = {}
             _lib.load().b200xf_ctx_destroy(self._ctx)
             self._ctx = None
+            self._symmetric = None
 
     def __del__(self):
         try:

@@ -85,13 +85,15 @@ def _rank_main(rank, world, port, out_dir, env):
     assert raised == sharded, "sharded Adam slots must not be readable before gather_optimizer_state()"
     model.gather_optimizer_state()
     m = model.get_slot_dict("adam_m"); v = model.get_slot_dict("adam_v")
+    assert b200xf._lib.load().b200xf_nvls_error(model._ctx) == 0
+    nvls = model._symmetric is not None
     # dropout: every replica draws its own masks (the rank is part of the key)
     hp_drop = dict(HP2, droput_rate=0.1)
     dm = b200xf.Transformer(**hp_drop, seed=2, device=f"cuda:{rank}")
     dm.trainable_variables
     strategy.attach(dm)
     mask = dm.dropout_mask(2, 64).cpu().numpy()
-    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), res=np.stack(res), mask=mask,
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), res=np.stack(res), mask=mask, nvls=np.array([int(nvls)]),
              **{"w|" + k.replace("/", "|"): a for k, a in w.items()}, **{"m|" + k.replace("/", "|"): a for k, a in m.items()},
              **{"v|" + k.replace("/", "|"): a for k, a in v.items()})
     dist.barrier()
@@ -117,8 +119,9 @@ def _oracle_run(world):
     return w0, oracle, grads, per_step
 
 
-MODES = [pytest.param({}, id="default-sharded-pipelined-trailing"), pytest.param({"B200XF_PIPELINED_UPDATE": "1"}, id="pipelined-all"),
-         pytest.param({"B200XF_PIPELINED_UPDATE": "0"}, id="sharded-chained"), pytest.param({"B200XF_SHARDED_UPDATE": "0"}, id="replicated-allreduce")]
+MODES = [pytest.param({"B200XF_NVLS": "1"}, id="nvls-fused-update"),
+         pytest.param({"B200XF_NVLS": "0"}, id="nccl-sharded-pipelined-trailing"), pytest.param({"B200XF_NVLS": "0", "B200XF_PIPELINED_UPDATE": "1"}, id="nccl-pipelined-all"),
+         pytest.param({"B200XF_NVLS": "0", "B200XF_PIPELINED_UPDATE": "0"}, id="nccl-sharded-chained"), pytest.param({"B200XF_SHARDED_UPDATE": "0"}, id="nccl-replicated-allreduce")]
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
@@ -129,6 +132,8 @@ def test_two_ranks_match_oracle_and_each_other(tmp_path, env):
     env = dict(env, B200XF_BUCKET_MB="1")
     mp.spawn(_rank_main, args=(world, _free_port(), str(tmp_path), env), nprocs=world, join=True)
     z = [np.load(tmp_path / f"rank{r}.npz") for r in range(world)]
+    if env.get("B200XF_NVLS") == "1":
+        assert int(z[0]["nvls"][0]) == 1, "the fused NVLS update was expected to be active on this box"
     names = [k for k in z[0].files if k[:2] in ("w|", "m|", "v|")]
     for k in names:  # mirrored variables and (after the gather) optimizer slots: identical on every replica
         assert np.array_equal(z[1][k], z[0][k]), k
