@@ -367,6 +367,7 @@ int Context::init(const b200xf_hparams& h, int dev, cudaStream_t s) {
   if (const char* e = getenv("B200XF_BUCKET_JOIN")) bucket_join = atoi(e) != 0;
   if (const char* e = getenv("B200XF_PIPELINED_UPDATE")) pipelined_update = atoi(e);  // 0 off, 1 every bucket, 2 the last two bucket closes
   if (const char* e = getenv("B200XF_COMM_SMS")) comm_sms = std::max(0, atoi(e));
+  if (const char* e = getenv("B200XF_BWD_GEMM_CTAS")) bwd_gemm_ctas = std::max(0, atoi(e));
   if (const char* e = getenv("B200XF_NVLS_CTAS")) nvls_ctas = std::max(1, atoi(e));
   if (const char* e = getenv("B200XF_NVLS_TAIL_CTAS")) nvls_tail_ctas = std::max(1, atoi(e));
   if (const char* e = getenv("B200XF_WEIGHT_PREFETCH")) weights_static = atoi(e);  // bit mask, see context.h
@@ -483,6 +484,7 @@ int Context::nvls_attach(void* grads_mc, void* params_mc, void* const* pads, int
   for (int r = 0; r < world_; ++r) { if (!pads[r]) return set_error("nvls_attach: null flag pad"); nvls.pad_peer[r] = static_cast<unsigned*>(pads[r]); }
   nvls.pad_local = nvls.pad_peer[rank_];
   nvls.rank = rank_; nvls.world = world_;
+  if (!getenv("B200XF_NVLS_CTAS")) nvls_ctas = std::max(16, 128 / world_);  // a rank's shard is 1/world of a bucket: 16 CTAs keep up on 8 replicas, 4 need 32
   B200XF_CUDA(cudaMemsetAsync(nvls_words, 0, 2 * sizeof(unsigned), stream));
   B200XF_CUDA(cudaStreamSynchronize(stream));
   drop_graphs();
@@ -551,6 +553,7 @@ int Context::join_side() {
 // pass; a persistent GEMM grid that counts on all 148 SMs then waits for them with its last CTAs.  Leaving those SMs
 // out of the backward GEMM grids costs the 128-tile problems nothing.
 int Context::backward_gemm_cap() const {
+  if (bwd_gemm_ctas > 0) return bwd_gemm_ctas;
   if (!comm || world <= 1 || comm_sms <= 0) return 0;
   return std::max(num_sms() / 2, num_sms() - comm_sms);
 }

@@ -116,6 +116,9 @@ struct Context {
   int weights_static = 3;
   int comm_sms = 0;  // SMs left to the collectives' kernels during backward (B200XF_COMM_SMS); 0 = GEMMs use every SM
   int backward_gemm_cap() const;
+  // B200XF_BWD_GEMM_CTAS: cap on the grids of the backward GEMMs, so that a data-gradient GEMM (compute stream) and a weight-
+  // gradient GEMM (side stream) can hold SMs at the same time, each with several tiles per CTA (0 = every SM; measured: DESIGN 4b)
+  int bwd_gemm_ctas = 0;
   bool bucket_bytes_set = false;  // B200XF_BUCKET_MB given
   bool bucket_join = true;  // a closing bucket makes the compute stream wait for the side stream (B200XF_BUCKET_JOIN)
   bool overlap_update = false;

@@ -396,6 +396,44 @@ __global__ void embed_bwd_kernel(const int* __restrict__ keys, const int* __rest
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// Sort of the (token id, position) pairs of one batch side in ONE CTA, for batches of up to kSortMax tokens: the combined key
+// (token << 13 | position) is unique, so a bitonic network (not stable by itself) yields the same order as a stable sort by
+// token: ascending token, positions ascending within a token -- the order the gradient rows are summed in (deterministic).
+// Replaces key extraction + a library radix sort (two launches) for the Transformer-base / -big batch sizes.
+constexpr int kSortMax = 8192, kSortThreads = 1024;
+__global__ void __launch_bounds__(kSortThreads)
+embed_sort_kernel(const long long* __restrict__ tokens, int* __restrict__ keys_out, int* __restrict__ vals_out, int n, int vocab) {
+  pdl_wait();
+  pdl_trigger();
+  __shared__ unsigned sk[kSortMax];
+  int m = 1;
+  while (m < n) m <<= 1;
+  for (int i = threadIdx.x; i < m; i += kSortThreads) {
+    unsigned key = 0xFFFFFFFFu;  // padding sorts last
+    if (i < n) {
+      const long long t = tokens[i];
+      const unsigned tok = (t >= 0 && t < vocab) ? unsigned(t) : unsigned(vocab);  // out-of-range ids sort after every real id and are skipped
+      key = (tok << 13) | unsigned(i);
+    }
+    sk[i] = key;
+  }
+  __syncthreads();
+  for (int k = 2; k <= m; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < m; i += kSortThreads) {
+        const int l = i ^ j;
+        if (l > i) {
+          const unsigned a = sk[i], b = sk[l];
+          const bool up = (i & k) == 0;
+          if ((a > b) == up) { sk[i] = b; sk[l] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  for (int i = threadIdx.x; i < n; i += kSortThreads) { keys_out[i] = int(sk[i] >> 13); vals_out[i] = int(sk[i] & 8191u); }
+}
+
 }  // namespace
 
 int embed_pe_fwd(const long long* tokens, const float* table, int vocab, const float* pe, bf16* out, int B, int S, int d,
@@ -428,10 +466,15 @@ int embed_bwd(const long long* tokens, const bf16* dx, float* dtable, int vocab,
   int* vals_out = reinterpret_cast<int*>(base + 3 * seg);
   void* temp = base + 4 * seg;
   size_t temp_bytes = scratch_bytes - 4 * seg;
-  B200XF_CUDA(launch_k(embed_keys_kernel, (n + 255) / 256, 256, 0, stream, tokens, keys_in, vals_in, n, vocab));
-  int bits = 1;
-  while ((1ll << bits) <= vocab) ++bits;
-  B200XF_CUDA(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, n, 0, bits, stream));
+  if (n <= kSortMax && vocab < (1 << 19)) {
+    B200XF_CUDA(launch_k(embed_sort_kernel, 1, kSortThreads, 0, stream, tokens, keys_out, vals_out, n, vocab));
+    count_launch(-1);  // one launch instead of two
+  } else {  // long-sequence batches: key extraction + device-wide radix sort
+    B200XF_CUDA(launch_k(embed_keys_kernel, (n + 255) / 256, 256, 0, stream, tokens, keys_in, vals_in, n, vocab));
+    int bits = 1;
+    while ((1ll << bits) <= vocab) ++bits;
+    B200XF_CUDA(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, n, 0, bits, stream));
+  }
   const int threads = min(256, max(32, (d / 4 + 31) / 32 * 32));
   B200XF_CUDA(launch_k(embed_bwd_kernel, n, threads, 0, stream, keys_out, vals_out, dx, dtable, n, d, vocab, sqrtf(float(d)), drop));
   B200XF_CUDA(cudaGetLastError());

@@ -116,10 +116,10 @@ class B200Strategy:
             dist.broadcast_object_list(uid, src=0)
             model.comm_init(uid[0], self.rank, self.world_size)
             # The fused NVLS update moves ~(1 + 1/W) bucket sizes per link direction where reduce-scatter + all-gather over
-            # point-to-point links move 2 (W-1)/W: it wins from 4 replicas up (measured: profiles/r02_nvls_update.md) and
-            # loses at 2.  B200XF_NVLS=1 / 0 forces it on / off.
+            # point-to-point links move 2 (W-1)/W, and it needs fewer SMs the smaller the shard: measured faster on 8 replicas
+            # (4.53 -> 4.21 ms/step), on par on 4, slower on 2 (profiles/r02_nvls_update.md).  B200XF_NVLS=1 / 0 forces it on / off.
             mode = os.environ.get("B200XF_NVLS", "auto")
-            if mode == "1" or (mode not in ("0", "1") and self.world_size >= 4):
+            if mode == "1" or (mode not in ("0", "1") and self.world_size >= 8):
                 self._attach_nvls(model)
         self._models.append(model)
         return model
