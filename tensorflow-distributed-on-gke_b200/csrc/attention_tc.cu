@@ -512,6 +512,225 @@ attn_fwd_tc_multi_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
   if (warp == 1) { ptx::tc_fence_after(); ptx::tmem_dealloc(tmem, 256); }
 }
 
+// ---------------------------------------------------------------------------------------------------------- forward, any length, two query tiles
+// One CTA per (256 queries, head, batch): two 128-query tiles A and B share every K/V tile that TMA brings in, and their
+// softmax passes take turns with the tensor core -- while one tile's 128 threads (one per row) exponentiate, the MMA thread
+// runs the other tile's P V and the next S = Q K^T.  A thread pulls its whole 128-column score row out of TMEM with four loads
+// behind ONE wait (TMEM round trips, not arithmetic, were what an earlier two-pass version spent its time on), finds the row
+// maximum, exponentiates, writes P.  O accumulates in TMEM across the key tiles; when a row's running maximum moves, the warp
+// rescales its O rows in place (tcgen05.ld / st) before the next P V is issued -- after the first few key tiles that is rare.
+// TMEM: S_A | S_B (128 columns each) | O_A | O_B (64 each).
+constexpr int kThreadsPP = 320;   // warp 0: TMA + MMA issue, warp 1: TMEM allocation, warps 2-5: tile A rows, warps 6-9: tile B rows
+constexpr int kSmemFwdPP = 2 * kTileBytes /*Q_A Q_B*/ + 4 * kTileBytes /*K V x2*/ + 2 * kPBytes /*P_A P_B*/ + 1024 + 4096;
+
+__global__ void __launch_bounds__(kThreadsPP, 1)
+attn_fwd_tc_pp_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
+                      const __grid_constant__ CUtensorMap tm_v, const TcArgs p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sQ = smem; uint8_t* sK = sQ + 2 * kTileBytes; uint8_t* sV = sK + 2 * kTileBytes; uint8_t* sP = sV + 2 * kTileBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * kPBytes);
+  uint64_t* bar_q = bars; uint64_t* kv_full = bars + 1; uint64_t* kv_empty = bars + 3;
+  uint64_t* s_ready = bars + 5; uint64_t* p_ready = bars + 7; uint64_t* o_ready = bars + 9;   // [2] each: tile A, tile B
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+  int* s_mask = reinterpret_cast<int*>(bars + 12);            // [2 tiles][2 stages][128]
+  int* any_flag = s_mask + 4 * kT;                             // [2 tiles][2 stages][4 warps]: some key of the tile is masked
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int q0 = (p.causal ? int(gridDim.x) - 1 - int(blockIdx.x) : int(blockIdx.x)) * 2 * kT;   // causal: the longest tiles first
+  const long long* toks = p.key_tokens + size_t(b) * p.Sk;
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tm_q); ptx::prefetch_tmap(&tm_k); ptx::prefetch_tmap(&tm_v);
+    ptx::mbar_init(bar_q, 1);
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1);
+      ptx::mbar_init(&s_ready[i], 1); ptx::mbar_init(&p_ready[i], 128); ptx::mbar_init(&o_ready[i], 1);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) { ptx::tmem_alloc(tmem_slot, 512); ptx::tmem_relinquish(); }
+  pdl_wait();
+  pdl_trigger();
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  // key tiles each query tile has to visit (a causal tile stops at its own diagonal; a tile past Sq visits none)
+  int nt[2];
+#pragma unroll
+  for (int g = 0; g < 2; ++g) {
+    const int qg = q0 + g * kT;
+    int kv_end = p.Sk;
+    if (p.causal && toks[0] != 0) kv_end = min(p.Sk, qg + kT);   // later key tiles are exactly zero-weight
+    nt[g] = qg < p.Sq ? (kv_end + kT - 1) / kT : 0;
+  }
+  const int ntiles = max(nt[0], nt[1]);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const uint32_t aQ = ptx::smem_u32(sQ), aP = ptx::smem_u32(sP);
+      constexpr uint32_t idesc_kk = ptx::make_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t idesc_km = ptx::make_idesc_bf16(128, 64, 0, 1);
+      auto load_kv = [&](int j) {
+        const int st = j & 1;
+        ptx::mbar_expect_tx(&kv_full[st], 2 * kTileBytes);
+        ptx::tma_load_2d(sK + st * kTileBytes, &tm_k, &kv_full[st], h * kD, b * p.Sk + j * kT);
+        ptx::tma_load_2d(sV + st * kTileBytes, &tm_v, &kv_full[st], h * kD, b * p.Sk + j * kT);
+      };
+      auto issue_s = [&](int g, int j) {   // S_g = Q_g K_j^T
+        const uint32_t aK = ptx::smem_u32(sK + (j & 1) * kTileBytes);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          ptx::umma_bf16(tmem + g * 128, ptx::make_smem_desc(aQ + g * kTileBytes + k * 32, 16, 1024), ptx::make_smem_desc(aK + k * 32, 16, 1024), idesc_kk, k > 0);
+        ptx::umma_commit(&s_ready[g]);
+      };
+      auto issue_pv = [&](int g, int j) {  // O_g (+)= P_g V_j
+        const uint32_t aV = ptx::smem_u32(sV + (j & 1) * kTileBytes);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          ptx::umma_bf16(tmem + 256 + g * 64, ptx::make_smem_desc(aP + g * kPBytes + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
+                         ptx::make_smem_desc(aV + k * 2048, kTileBytes, 1024), idesc_km, (j > 0 || k > 0) ? 1u : 0u);
+        ptx::umma_commit(&o_ready[g]);
+      };
+      ptx::mbar_expect_tx(bar_q, (nt[1] > 0 ? 2 : 1) * kTileBytes);
+      ptx::tma_load_2d(sQ, &tm_q, bar_q, h * kD, b * p.Sq + q0);
+      if (nt[1] > 0) ptx::tma_load_2d(sQ + kTileBytes, &tm_q, bar_q, h * kD, b * p.Sq + q0 + kT);
+      if (ntiles > 0) load_kv(0);
+      ptx::mbar_wait(bar_q, 0);
+      if (ntiles > 0) {
+        ptx::mbar_wait(&kv_full[0], 0);
+        ptx::tc_fence_after();
+        if (nt[0] > 0) issue_s(0, 0);
+        if (nt[1] > 0) issue_s(1, 0);
+        if (ntiles > 1) load_kv(1);
+      }
+      for (int j = 0; j < ntiles; ++j) {
+        const bool more = j + 1 < ntiles;
+        if (more) { ptx::mbar_wait(&kv_full[(j + 1) & 1], ((j + 1) >> 1) & 1); ptx::tc_fence_after(); }
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          if (j < nt[g]) {
+            ptx::mbar_wait(&p_ready[g], j & 1);       // tile g has read S_g(j), rescaled O_g if needed and written P_g(j)
+            ptx::tc_fence_after();
+            issue_pv(g, j);
+            if (j + 1 < nt[g]) issue_s(g, j + 1);      // its next S, while the other tile is in its softmax
+          }
+        }
+        ptx::umma_commit(&kv_empty[j & 1]);            // K_j / V_j may be overwritten once the MMAs above retire
+        if (j + 2 < ntiles) {
+          ptx::mbar_wait(&kv_empty[j & 1], (j >> 1) & 1);
+          load_kv(j + 2);
+        }
+      }
+    }
+  } else if (warp >= 2) {
+    const int g = (warp - 2) >> 2;                      // 0: tile A, 1: tile B
+    const int quarter = warp & 3;
+    const int i = quarter * 32 + lane;                  // row within the tile
+    const uint32_t lane_base = uint32_t(quarter * 32) << 16;
+    const int e = (threadIdx.x - 64) & 127;
+    const int qg = q0 + g * kT;
+    const bool row_ok = qg + i < p.Sq;
+    const uint32_t tS = tmem + g * 128, tO = tmem + 256 + g * 64;
+    uint8_t* sPg = sP + g * kPBytes;
+    float m = -INFINITY, l = 0.f;
+    for (int j = 0; j < nt[g]; ++j) {
+      const int k0 = j * kT;
+      int* mask = s_mask + (g * 2 + (j & 1)) * kT;
+      const int mk_mine = (k0 + e >= p.Sk) ? 2 : (toks[k0 + e] == 0 ? 1 : 0);
+      mask[e] = mk_mine;
+      // a key tile without PAD keys, inside Sk and (when causal) wholly below this query tile's diagonal needs no per-key test
+      if (lane == 0) any_flag[(g * 2 + (j & 1)) * 4 + quarter] = 0;
+      __syncwarp();
+      if (mk_mine != 0) any_flag[(g * 2 + (j & 1)) * 4 + quarter] = 1;
+      if (g == 0) asm volatile("bar.sync 1, 128;" ::: "memory"); else asm volatile("bar.sync 2, 128;" ::: "memory");
+      const int* af = any_flag + (g * 2 + (j & 1)) * 4;
+      const bool plain = (af[0] | af[1] | af[2] | af[3]) == 0 && !(p.causal && k0 + kT - 1 > qg);
+      ptx::mbar_wait(&s_ready[g], j & 1);
+      ptx::tc_fence_after();
+      uint32_t sv[128];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) ptx::tmem_ld_32x32(tS + lane_base + c * 32, sv + c * 32);
+      ptx::tmem_ld_wait();
+      float mx = -INFINITY;
+      if (plain) {
+#pragma unroll
+        for (int key = 0; key < 128; key += 2) mx = fmaxf(mx, fmaxf(__uint_as_float(sv[key]), __uint_as_float(sv[key + 1])));
+        mx *= p.scale_log2;                              // the scale is positive: max(s) * scale = max(s * scale)
+      } else {
+#pragma unroll
+        for (int key = 0; key < 128; ++key) {
+          const int mk = mask[key];
+          float v = __uint_as_float(sv[key]) * p.scale_log2;
+          if (mk == 1 || (p.causal && k0 + key > qg + i)) v = kMasked;
+          if (mk == 2) v = -INFINITY;
+          sv[key] = __float_as_uint(v);
+          mx = fmaxf(mx, v);
+        }
+      }
+      const float m_new = fmaxf(m, mx);                 // finite: the first tile always holds a real key
+      const float corr = ptx::fast_exp2(m - m_new);
+      if (j > 0) {
+        ptx::mbar_wait(&o_ready[g], (j - 1) & 1);       // P V of the previous key tile is in TMEM (and has read the P buffer)
+        ptx::tc_fence_after();
+        if (__any_sync(0xffffffffu, corr != 1.0f)) {    // some row's maximum moved: rescale this warp's O rows in place
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            uint32_t ov[32];
+            ptx::tmem_ld_32x32(tO + lane_base + c * 32, ov);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int t = 0; t < 32; ++t) ov[t] = __float_as_uint(__uint_as_float(ov[t]) * corr);
+            ptx::tmem_st_32x32(tO + lane_base + c * 32, ov);
+          }
+          ptx::tmem_st_wait();
+        }
+      }
+      float sum = 0.f;
+      const float sc = plain ? p.scale_log2 : 1.0f;     // plain tiles still hold the raw scores
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float f[32];
+#pragma unroll
+        for (int t = 0; t < 32; ++t) { f[t] = ptx::fast_exp2(fmaf(__uint_as_float(sv[c * 32 + t]), sc, -m_new)); sum += f[t]; }   // exp2(-inf) = 0 past Sk
+        store_row32(sPg, i, c * 32, f);
+      }
+      ptx::tc_fence_before();
+      ptx::fence_proxy_async();
+      ptx::mbar_arrive(&p_ready[g]);
+      l = l * corr + sum;
+      m = m_new;
+    }
+    if (nt[g] > 0) {
+      ptx::mbar_wait(&o_ready[g], (nt[g] - 1) & 1);
+      ptx::tc_fence_after();
+      const float inv = 1.0f / l;
+      bf16* dst = p.o + (size_t(b) * p.Sq + qg + i) * p.ldo + h * kD;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        float ot[32];
+        tmem_ld32(tO + lane_base + c * 32, ot);
+        if (row_ok) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint4 u;
+            u.x = ptx::pack_bf16x2(ot[q * 8] * inv, ot[q * 8 + 1] * inv); u.y = ptx::pack_bf16x2(ot[q * 8 + 2] * inv, ot[q * 8 + 3] * inv);
+            u.z = ptx::pack_bf16x2(ot[q * 8 + 4] * inv, ot[q * 8 + 5] * inv); u.w = ptx::pack_bf16x2(ot[q * 8 + 6] * inv, ot[q * 8 + 7] * inv);
+            *reinterpret_cast<uint4*>(dst + c * 32 + q * 8) = u;
+          }
+        }
+      }
+      if (row_ok && p.lse) reinterpret_cast<float2*>(p.lse)[(size_t(b) * p.H + h) * p.Sq + qg + i] = make_float2(m, log2f(l));
+      ptx::tc_fence_before();
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { ptx::tc_fence_after(); ptx::tmem_dealloc(tmem, 512); }
+}
+
 // ---------------------------------------------------------------------------------------------------------- backward, any length
 // One CTA per (128-key tile, head, batch) walks the 128-query tiles that can see those keys.  Per (q tile, kv tile) pair:
 //   S = Q K^T, dP = dO V^T -> threads: P = exp2(s - m_i - log2 l_i), dS = P (dP - delta_i) -> smem ->
@@ -758,13 +977,18 @@ attn_bwd_dq_out_kernel(const float* __restrict__ dq_acc, bf16* __restrict__ dq, 
 
 }  // namespace
 
-// Measured on B200 (scripts/kernel_bench.py long / big): this forward is on par with the mma.sync kernel (63 vs 67 us causal,
-// 91 vs 89 us non-causal at B8 H8 S1024; 30 vs 26 us at S256) because one CTA serialises S -> softmax -> PV, so it is opt-in
-// (B200XF_ATTENTION_TC_FWD_MULTI=1, read once) until it ping-pongs two query tiles per CTA.
+// Sequences longer than one tile (head size 64): the two-query-tile kernel above (B200XF_ATTENTION_TC_FWD_MULTI: 1 = default,
+// 2 = the earlier one-tile-per-CTA tcgen05 kernel, which only ties with the mma.sync kernel because one CTA serialises
+// S -> softmax -> P V; 0 = the mma.sync kernel).
+static int fwd_multi_mode() {
+  static int mode = -1;  // read once
+  if (mode < 0) { const char* e = getenv("B200XF_ATTENTION_TC_FWD_MULTI"); mode = e ? std::max(0, std::min(2, atoi(e))) : 1; }
+  return mode;
+}
 bool attention_tc_fwd_multi_supported(const AttnArgs& a) {
-  static int enabled = -1;  // read once
-  if (enabled < 0) { const char* e = getenv("B200XF_ATTENTION_TC_FWD_MULTI"); enabled = (e && atoi(e) != 0) ? 1 : 0; }
-  return enabled && a.dk == kD && a.Sq > 0 && a.Sk > 0;
+  static int enabled = -1;
+  if (enabled < 0) { const char* e = getenv("B200XF_ATTENTION_TC"); enabled = (e && atoi(e) == 0) ? 0 : 1; }
+  return enabled && fwd_multi_mode() != 0 && a.dk == kD && a.Sq > 0 && a.Sk > 0;
 }
 
 int attention_fwd_tc_multi(const AttnArgs& a, cudaStream_t stream) {
@@ -777,6 +1001,12 @@ int attention_fwd_tc_multi(const AttnArgs& a, cudaStream_t stream) {
   p.key_tokens = a.key_tokens; p.o = a.o; p.ldo = a.ldo; p.lse = a.lse;
   p.H = a.H; p.Sq = a.Sq; p.Sk = a.Sk; p.causal = a.causal;
   p.scale = 1.0f / sqrtf(float(a.dk)); p.scale_log2 = p.scale * kLog2e;
+  if (fwd_multi_mode() == 1) {
+    B200XF_TRY(ensure_dynamic_smem(attn_fwd_tc_pp_kernel, kSmemFwdPP));
+    B200XF_CUDA(launch_k(attn_fwd_tc_pp_kernel, dim3((a.Sq + 2 * kT - 1) / (2 * kT), a.H, a.B), kThreadsPP, kSmemFwdPP, stream, tq, tk, tv, p));
+    count_launch();
+    return 0;
+  }
   B200XF_TRY(ensure_dynamic_smem(attn_fwd_tc_multi_kernel, kSmemFwdMulti));
   B200XF_CUDA(launch_k(attn_fwd_tc_multi_kernel, dim3((a.Sq + kT - 1) / kT, a.H, a.B), kThreadsMulti, kSmemFwdMulti, stream, tq, tk, tv, p));
   count_launch();
