@@ -396,42 +396,82 @@ __global__ void embed_bwd_kernel(const int* __restrict__ keys, const int* __rest
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-// Sort of the (token id, position) pairs of one batch side in ONE CTA, for batches of up to kSortMax tokens: the combined key
+// Sort of the (token id, position) pairs of one batch side in ONE CTA, for batches of up to kSortMax (4096) tokens: the combined key
 // (token << 13 | position) is unique, so a bitonic network (not stable by itself) yields the same order as a stable sort by
 // token: ascending token, positions ascending within a token -- the order the gradient rows are summed in (deterministic).
 // Replaces key extraction + a library radix sort (two launches) for the Transformer-base / -big batch sizes.
-constexpr int kSortMax = 8192, kSortThreads = 1024;
+constexpr int kSortMax = 4096, kSortThreads = 1024;
+// Element e lives in thread (e % 1024), register (e / 1024).  Compare-exchange distances below 32 run as warp shuffles, distances
+// of 1024 and more inside a thread's own registers; only the distances 32..512 go through shared memory (one barrier each).
+template <int R>
+__device__ __forceinline__ void bitonic_sort_regs(unsigned (&x)[R], unsigned* buf) {
+  const int t = threadIdx.x;
+  int flip = 0;
+  for (int k = 2; k <= R * kSortThreads; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      if (j >= kSortThreads) {
+        const int jr = j / kSortThreads;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const int l = r ^ jr;
+          if (l > r) {
+            const bool up = ((r * kSortThreads + t) & k) == 0;
+            const unsigned a = x[r], b = x[l];
+            if ((a > b) == up) { x[r] = b; x[l] = a; }
+          }
+        }
+      } else if (j >= 32) {
+        unsigned* bb = buf + flip * (R * kSortThreads);
+        flip ^= 1;
+#pragma unroll
+        for (int r = 0; r < R; ++r) bb[r * kSortThreads + t] = x[r];
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const int i = r * kSortThreads + t;
+          const unsigned other = bb[i ^ j];
+          const bool up = (i & k) == 0, lower = (i & j) == 0;
+          const unsigned mn = min(x[r], other), mx = max(x[r], other);
+          x[r] = (lower == up) ? mn : mx;
+        }
+      } else {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const int i = r * kSortThreads + t;
+          const unsigned other = __shfl_xor_sync(0xffffffffu, x[r], j);
+          const bool up = (i & k) == 0, lower = (i & j) == 0;
+          const unsigned mn = min(x[r], other), mx = max(x[r], other);
+          x[r] = (lower == up) ? mn : mx;
+        }
+      }
+    }
+  }
+}
+
+template <int R>
 __global__ void __launch_bounds__(kSortThreads)
 embed_sort_kernel(const long long* __restrict__ tokens, int* __restrict__ keys_out, int* __restrict__ vals_out, int n, int vocab) {
   pdl_wait();
   pdl_trigger();
-  __shared__ unsigned sk[kSortMax];
-  int m = 1;
-  while (m < n) m <<= 1;
-  for (int i = threadIdx.x; i < m; i += kSortThreads) {
+  __shared__ unsigned buf[2 * R * kSortThreads];
+  unsigned x[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int i = r * kSortThreads + threadIdx.x;
     unsigned key = 0xFFFFFFFFu;  // padding sorts last
     if (i < n) {
-      const long long t = tokens[i];
-      const unsigned tok = (t >= 0 && t < vocab) ? unsigned(t) : unsigned(vocab);  // out-of-range ids sort after every real id and are skipped
+      const long long tk = tokens[i];
+      const unsigned tok = (tk >= 0 && tk < vocab) ? unsigned(tk) : unsigned(vocab);  // out-of-range ids sort after every real id and are skipped
       key = (tok << 13) | unsigned(i);
     }
-    sk[i] = key;
+    x[r] = key;
   }
-  __syncthreads();
-  for (int k = 2; k <= m; k <<= 1) {
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int i = threadIdx.x; i < m; i += kSortThreads) {
-        const int l = i ^ j;
-        if (l > i) {
-          const unsigned a = sk[i], b = sk[l];
-          const bool up = (i & k) == 0;
-          if ((a > b) == up) { sk[i] = b; sk[l] = a; }
-        }
-      }
-      __syncthreads();
-    }
+  bitonic_sort_regs<R>(x, buf);
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int i = r * kSortThreads + threadIdx.x;
+    if (i < n) { keys_out[i] = int(x[r] >> 13); vals_out[i] = int(x[r] & 8191u); }
   }
-  for (int i = threadIdx.x; i < n; i += kSortThreads) { keys_out[i] = int(sk[i] >> 13); vals_out[i] = int(sk[i] & 8191u); }
 }
 
 }  // namespace
@@ -467,7 +507,9 @@ int embed_bwd(const long long* tokens, const bf16* dx, float* dtable, int vocab,
   void* temp = base + 4 * seg;
   size_t temp_bytes = scratch_bytes - 4 * seg;
   if (n <= kSortMax && vocab < (1 << 19)) {
-    B200XF_CUDA(launch_k(embed_sort_kernel, 1, kSortThreads, 0, stream, tokens, keys_out, vals_out, n, vocab));
+    if (n <= 1024) B200XF_CUDA(launch_k(embed_sort_kernel<1>, 1, kSortThreads, 0, stream, tokens, keys_out, vals_out, n, vocab));
+    else if (n <= 2048) B200XF_CUDA(launch_k(embed_sort_kernel<2>, 1, kSortThreads, 0, stream, tokens, keys_out, vals_out, n, vocab));
+    else B200XF_CUDA(launch_k(embed_sort_kernel<4>, 1, kSortThreads, 0, stream, tokens, keys_out, vals_out, n, vocab));
     count_launch(-1);  // one launch instead of two
   } else {  // long-sequence batches: key extraction + device-wide radix sort
     B200XF_CUDA(launch_k(embed_keys_kernel, (n + 255) / 256, 256, 0, stream, tokens, keys_in, vals_in, n, vocab));
