@@ -656,9 +656,12 @@ attn_fwd_tc_pp_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       ptx::tmem_ld_wait();
       float mx = -INFINITY;
       if (plain) {
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four independent chains: a single one is 64 dependent steps
 #pragma unroll
-        for (int key = 0; key < 128; key += 2) mx = fmaxf(mx, fmaxf(__uint_as_float(sv[key]), __uint_as_float(sv[key + 1])));
-        mx *= p.scale_log2;                              // the scale is positive: max(s) * scale = max(s * scale)
+        for (int key = 0; key < 128; key += 8)
+#pragma unroll
+          for (int u = 0; u < 4; ++u) m4[u] = fmaxf(m4[u], fmaxf(__uint_as_float(sv[key + 2 * u]), __uint_as_float(sv[key + 2 * u + 1])));
+        mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale_log2;   // the scale is positive: max(s) * scale = max(s * scale)
       } else {
 #pragma unroll
         for (int key = 0; key < 128; ++key) {
@@ -688,15 +691,16 @@ attn_fwd_tc_pp_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
           ptx::tmem_st_wait();
         }
       }
-      float sum = 0.f;
+      float s4[4] = {0.f, 0.f, 0.f, 0.f};               // independent partial sums (one chain would be 128 dependent adds)
       const float sc = plain ? p.scale_log2 : 1.0f;     // plain tiles still hold the raw scores
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         float f[32];
 #pragma unroll
-        for (int t = 0; t < 32; ++t) { f[t] = ptx::fast_exp2(fmaf(__uint_as_float(sv[c * 32 + t]), sc, -m_new)); sum += f[t]; }   // exp2(-inf) = 0 past Sk
+        for (int t = 0; t < 32; ++t) { f[t] = ptx::fast_exp2(fmaf(__uint_as_float(sv[c * 32 + t]), sc, -m_new)); s4[t & 3] += f[t]; }   // exp2(-inf) = 0 past Sk
         store_row32(sPg, i, c * 32, f);
       }
+      const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
       ptx::tc_fence_before();
       ptx::fence_proxy_async();
       ptx::mbar_arrive(&p_ready[g]);
