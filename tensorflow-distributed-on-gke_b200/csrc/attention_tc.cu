@@ -517,11 +517,13 @@ attn_fwd_tc_multi_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
 // softmax passes take turns with the tensor core -- while one tile's 128 threads (one per row) exponentiate, the MMA thread
 // runs the other tile's P V and the next S = Q K^T.  A thread pulls its whole 128-column score row out of TMEM with four loads
 // behind ONE wait (TMEM round trips, not arithmetic, were what an earlier two-pass version spent its time on), finds the row
-// maximum, exponentiates, writes P.  O accumulates in TMEM across the key tiles; when a row's running maximum moves, the warp
+// maximum, exponentiates, and writes P (bf16) back into TMEM over the score columns it has consumed: the P V product takes its A
+// operand straight from TMEM (no shared-memory round trip, no bank conflicts, no proxy fence).  O accumulates in TMEM across the key tiles; when a row's running maximum moves, the warp
 // rescales its O rows in place (tcgen05.ld / st) before the next P V is issued -- after the first few key tiles that is rare.
 // TMEM: S_A | S_B (128 columns each) | O_A | O_B (64 each).
+constexpr bool kPInTmem = true;   // P as the tensor core's A operand straight from TMEM (false: through shared memory)
 constexpr int kThreadsPP = 320;   // warp 0: TMA + MMA issue, warp 1: TMEM allocation, warps 2-5: tile A rows, warps 6-9: tile B rows
-constexpr int kSmemFwdPP = 2 * kTileBytes /*Q_A Q_B*/ + 4 * kTileBytes /*K V x2*/ + 2 * kPBytes /*P_A P_B*/ + 1024 + 4096;
+constexpr int kSmemFwdPP = 2 * kTileBytes /*Q_A Q_B*/ + 4 * kTileBytes /*K V x2*/ + (kPInTmem ? 0 : 2 * kPBytes) /*P_A P_B*/ + 1024 + 4096;
 
 __global__ void __launch_bounds__(kThreadsPP, 1)
 attn_fwd_tc_pp_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
@@ -529,7 +531,7 @@ attn_fwd_tc_pp_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sQ = smem; uint8_t* sK = sQ + 2 * kTileBytes; uint8_t* sV = sK + 2 * kTileBytes; uint8_t* sP = sV + 2 * kTileBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * kPBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + (kPInTmem ? 0 : 2 * kPBytes));
   uint64_t* bar_q = bars; uint64_t* kv_full = bars + 1; uint64_t* kv_empty = bars + 3;
   uint64_t* s_ready = bars + 5; uint64_t* p_ready = bars + 7; uint64_t* o_ready = bars + 9;   // [2] each: tile A, tile B
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
@@ -589,9 +591,13 @@ attn_fwd_tc_pp_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       auto issue_pv = [&](int g, int j) {  // O_g (+)= P_g V_j
         const uint32_t aV = ptx::smem_u32(sV + (j & 1) * kTileBytes);
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          ptx::umma_bf16(tmem + 256 + g * 64, ptx::make_smem_desc(aP + g * kPBytes + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
-                         ptx::make_smem_desc(aV + k * 2048, kTileBytes, 1024), idesc_km, (j > 0 || k > 0) ? 1u : 0u);
+        for (int k = 0; k < 8; ++k) {
+          if (kPInTmem)   // P_g sits in the first 64 columns of S_g's TMEM region: 16 keys = 8 columns per MMA
+            ptx::umma_bf16_ts(tmem + 256 + g * 64, tmem + g * 128 + k * 8, ptx::make_smem_desc(aV + k * 2048, kTileBytes, 1024), idesc_km, (j > 0 || k > 0) ? 1u : 0u);
+          else
+            ptx::umma_bf16(tmem + 256 + g * 64, ptx::make_smem_desc(aP + g * kPBytes + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
+                           ptx::make_smem_desc(aV + k * 2048, kTileBytes, 1024), idesc_km, (j > 0 || k > 0) ? 1u : 0u);
+        }
         ptx::umma_commit(&o_ready[g]);
       };
       ptx::mbar_expect_tx(bar_q, (nt[1] > 0 ? 2 : 1) * kTileBytes);
@@ -693,16 +699,34 @@ attn_fwd_tc_pp_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       }
       float s4[4] = {0.f, 0.f, 0.f, 0.f};               // independent partial sums (one chain would be 128 dependent adds)
       const float sc = plain ? p.scale_log2 : 1.0f;     // plain tiles still hold the raw scores
+      if (kPInTmem) {
+        // P (bf16 pairs) goes back into TMEM over the score columns this thread has just consumed: its own lane, no shared-memory
+        // traffic (a row-per-thread store into the swizzled operand tile is a 4-way bank conflict), no proxy fence
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        float f[32];
+        for (int c = 0; c < 2; ++c) {
+          uint32_t pk[32];
 #pragma unroll
-        for (int t = 0; t < 32; ++t) { f[t] = ptx::fast_exp2(fmaf(__uint_as_float(sv[c * 32 + t]), sc, -m_new)); s4[t & 3] += f[t]; }   // exp2(-inf) = 0 past Sk
-        store_row32(sPg, i, c * 32, f);
+          for (int t = 0; t < 32; ++t) {
+            const float a = ptx::fast_exp2(fmaf(__uint_as_float(sv[c * 64 + 2 * t]), sc, -m_new));
+            const float b2 = ptx::fast_exp2(fmaf(__uint_as_float(sv[c * 64 + 2 * t + 1]), sc, -m_new));
+            s4[t & 1] += a; s4[2 + (t & 1)] += b2;
+            pk[t] = ptx::pack_bf16x2(a, b2);
+          }
+          ptx::tmem_st_32x32(tS + lane_base + c * 32, pk);
+        }
+        ptx::tmem_st_wait();
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          float f[32];
+#pragma unroll
+          for (int t = 0; t < 32; ++t) { f[t] = ptx::fast_exp2(fmaf(__uint_as_float(sv[c * 32 + t]), sc, -m_new)); s4[t & 3] += f[t]; }   // exp2(-inf) = 0 past Sk
+          store_row32(sPg, i, c * 32, f);
+        }
+        ptx::fence_proxy_async();
       }
       const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
       ptx::tc_fence_before();
-      ptx::fence_proxy_async();
       ptx::mbar_arrive(&p_ready[g]);
       l = l * corr + sum;
       m = m_new;
