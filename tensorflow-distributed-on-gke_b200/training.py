@@ -117,9 +117,9 @@ class B200Strategy:
             model.comm_init(uid[0], self.rank, self.world_size)
             # The fused NVLS update moves ~(1 + 1/W) bucket sizes per link direction where reduce-scatter + all-gather over
             # point-to-point links move 2 (W-1)/W, and it needs fewer SMs the smaller the shard: measured faster on 8 replicas
-            # (4.53 -> 4.21 ms/step), on par on 4, slower on 2 (profiles/r02_nvls_update.md).  B200XF_NVLS=1 / 0 forces it on / off.
+            # (4.55 -> 4.19 ms/step) and on 4 (4.48 -> 4.33), slower on 2 (profiles/r02_nvls_update.md).  B200XF_NVLS=1 / 0 forces it on / off.
             mode = os.environ.get("B200XF_NVLS", "auto")
-            if mode == "1" or (mode not in ("0", "1") and self.world_size >= 8):
+            if mode == "1" or (mode not in ("0", "1") and self.world_size >= 4):
                 self._attach_nvls(model)
         self._models.append(model)
         return model
