@@ -163,11 +163,16 @@ int b200xf_optimizer_state_complete(b200xf_ctx* ctx);
  *   b200xf_use_external_state  moves weights and gradients into caller-owned DEVICE buffers (256-byte aligned, param_total
  *                              floats each; contents are carried over; b200xf_param_ptr / b200xf_grad_ptr change);
  *   b200xf_nvls_attach         after b200xf_comm_init: the multicast addresses of those two buffers and, per rank, the address
- *                              of a zeroed symmetric flag pad of >= 256 bytes as mapped into this process; world <= 8;
+ *                              of a zeroed symmetric flag pad of >= 256 bytes as mapped into this process; world <= 8.
+ *                              point_to_point != 0 selects the variant of the same kernel that reads every replica's gradients and
+ *                              writes every replica's weights through the per-rank peer mappings (grads_peers / params_peers, own
+ *                              buffers at [rank]) instead of multimem: (W-1)/W bucket sizes per link direction instead of ~(1 + 1/W),
+ *                              the better choice below 8 replicas; the multicast addresses may then be NULL;
  *   b200xf_nvls_error          non-zero once a replica failed to arrive at a cross-replica flag within ~10 s.
  * No counterpart in the reference beyond cluster/cluster.py:66: the collective is implicit there. */
 int b200xf_use_external_state(b200xf_ctx* ctx, float* params, float* grads);
-int b200xf_nvls_attach(b200xf_ctx* ctx, void* grads_multicast, void* params_multicast, void* const* flag_pads, int rank, int world);
+int b200xf_nvls_attach(b200xf_ctx* ctx, void* grads_multicast, void* params_multicast, void* const* flag_pads, void* const* grads_peers,
+                       void* const* params_peers, int point_to_point, int rank, int world);
 int b200xf_nvls_error(b200xf_ctx* ctx);
 /* Debug / benchmark aid: one fused update of the flat range [begin, begin + count) (count a multiple of 64 * world) on `ctas`
  * CTAs, optionally followed by the bf16 refresh / gradient clear; every replica must call it with the same arguments. */

@@ -68,7 +68,7 @@ SIGNATURES = {
     "b200xf_comm_init": (_I, [_P, _P, _I, _I]),
     "b200xf_comm_destroy": (_I, [_P]),
     "b200xf_use_external_state": (_I, [_P, _P, _P]),
-    "b200xf_nvls_attach": (_I, [_P, _P, _P, C.POINTER(_P), _I, _I]),
+    "b200xf_nvls_attach": (_I, [_P, _P, _P, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), _I, _I, _I]),
     "b200xf_nvls_error": (_I, [_P]),
     "b200xf_debug_nvls_update": (_I, [_P, _L, _L, _I, _I]),
     "b200xf_gather_optimizer_state": (_I, [_P]),

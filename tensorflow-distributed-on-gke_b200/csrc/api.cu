@@ -155,9 +155,10 @@ int b200xf_use_external_state(b200xf_ctx* ctx, float* params, float* grads) {
   if (!ctx) return set_error("null ctx");
   return ctx->c.use_external_state(params, grads);
 }
-int b200xf_nvls_attach(b200xf_ctx* ctx, void* grads_multicast, void* params_multicast, void* const* flag_pads, int rank, int world) {
+int b200xf_nvls_attach(b200xf_ctx* ctx, void* grads_multicast, void* params_multicast, void* const* flag_pads, void* const* grads_peers,
+                       void* const* params_peers, int point_to_point, int rank, int world) {
   if (!ctx) return set_error("null ctx");
-  return ctx->c.nvls_attach(grads_multicast, params_multicast, flag_pads, rank, world);
+  return ctx->c.nvls_attach(grads_multicast, params_multicast, flag_pads, grads_peers, params_peers, point_to_point, rank, world);
 }
 int b200xf_debug_nvls_update(b200xf_ctx* ctx, int64_t begin, int64_t count, int ctas, int refresh) {
   if (!ctx || !ctx->c.nvls_on) return set_error("debug_nvls_update: the NVLS update is not attached");

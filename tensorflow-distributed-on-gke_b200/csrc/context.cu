@@ -474,12 +474,21 @@ int Context::use_external_state(float* params_ext, float* grads_ext) {
   return 0;
 }
 
-int Context::nvls_attach(void* grads_mc, void* params_mc, void* const* pads, int rank_, int world_) {
+int Context::nvls_attach(void* grads_mc, void* params_mc, void* const* pads, void* const* grads_peers, void* const* params_peers, int p2p,
+                         int rank_, int world_) {
   if (!comm || rank_ != rank || world_ != world) return set_error("nvls_attach: attach the communicator first (same rank / world)");
   if (!external_state) return set_error("nvls_attach: parameters and gradients must live in symmetric memory (use_external_state)");
   if (world_ < 2 || world_ > kNvlsMaxWorld) return set_error("nvls_attach: world of %d unsupported (2..%d)", world_, kNvlsMaxWorld);
-  if (!grads_mc || !params_mc || !pads) return set_error("nvls_attach: null multicast mapping");
+  if (!pads) return set_error("nvls_attach: null flag pads");
+  if (p2p ? (!grads_peers || !params_peers) : (!grads_mc || !params_mc)) return set_error("nvls_attach: null %s mapping", p2p ? "peer" : "multicast");
   nvls = NvlsComm();
+  nvls.p2p = p2p ? 1 : 0;
+  if (grads_peers && params_peers)
+    for (int r = 0; r < world_; ++r) {
+      if (p2p && (!grads_peers[r] || !params_peers[r])) return set_error("nvls_attach: null peer mapping");
+      nvls.grads_peer[r] = static_cast<float*>(grads_peers[r]); nvls.params_peer[r] = static_cast<float*>(params_peers[r]);
+    }
+  if (p2p && (nvls.grads_peer[rank_] != grads || nvls.params_peer[rank_] != params)) return set_error("nvls_attach: this rank's peer mapping is not its own buffer");
   nvls.grads_mc = static_cast<float*>(grads_mc); nvls.params_mc = static_cast<float*>(params_mc);
   for (int r = 0; r < world_; ++r) { if (!pads[r]) return set_error("nvls_attach: null flag pad"); nvls.pad_peer[r] = static_cast<unsigned*>(pads[r]); }
   nvls.pad_local = nvls.pad_peer[rank_];

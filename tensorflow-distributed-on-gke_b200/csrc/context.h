@@ -131,7 +131,7 @@ struct Context {
   NvlsComm nvls; bool nvls_on = false;
   unsigned* nvls_words = nullptr;        // [0] launch counter of the update kernels, [1] CTA counter
   int nvls_ctas = 16, nvls_tail_ctas = 64;  // CTAs of the update kernel under backward / for the buckets that close after it (B200XF_NVLS_CTAS, _TAIL_CTAS)
-  int nvls_attach(void* grads_mc, void* params_mc, void* const* pads, int rank_, int world_);
+  int nvls_attach(void* grads_mc, void* params_mc, void* const* pads, void* const* grads_peers, void* const* params_peers, int p2p, int rank_, int world_);
   ~Context();
   int init(const b200xf_hparams& h, int dev, cudaStream_t s);
   void build_layout();

@@ -13,6 +13,11 @@ constexpr int kNvlsReady = 0, kNvlsDone = 16, kNvlsError = 32, kNvlsPadWords = 6
 struct NvlsComm {
   float* grads_mc = nullptr;    // multicast mapping of the flat gradient buffer (a load reduces over every replica's copy)
   float* params_mc = nullptr;   // multicast mapping of the flat fp32 weights (a store lands in every replica's copy)
+  // the same two buffers of every replica as mapped into this process (own ones included): the point-to-point variant of the
+  // update reads its shard of the gradients from each replica in turn and writes the new weights into each replica's copy
+  float* grads_peer[kNvlsMaxWorld] = {nullptr};
+  float* params_peer[kNvlsMaxWorld] = {nullptr};
+  int p2p = 0;                                   // 1: point-to-point loads / stores instead of multimem (fewer bytes per link below 8 replicas)
   unsigned* pad_local = nullptr;                 // this replica's flag pad
   unsigned* pad_peer[kNvlsMaxWorld] = {nullptr}; // every replica's flag pad as mapped into this process (own one included)
   int rank = 0, world = 1;

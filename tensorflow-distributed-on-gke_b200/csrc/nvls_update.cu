@@ -6,6 +6,9 @@
 //   Adam           : applies the TF-form update (same arithmetic as adam_kernel) to its shard with its local m / v,
 //   all-gather     : writes the updated fp32 weights to EVERY replica with multimem.st (the switch replicates the store).
 //
+// Below 8 replicas a point-to-point variant of the same kernel (plain loads from every replica's gradients, plain stores into every
+// replica's weights, over the peer mappings of the same symmetric buffers) moves fewer bytes per link: (W-1)/W bucket sizes per
+// direction against ~(1 + 1/W) through the switch.
 // Inbound (reduce) and outbound (broadcast) traffic run concurrently on the two directions of the links, where the
 // NCCL sequence reduce-scatter -> adam -> all-gather runs them one after the other.  The flat gradient and parameter buffers
 // live in symmetric memory with a multicast mapping (allocated by the host side, torch.distributed._symmetric_memory).
@@ -58,6 +61,7 @@ constexpr int kUnroll = 8;   // independent 16-byte multimem loads in flight per
 constexpr int kThreadsNvls = 512;
 
 // grid-stride over the shard's float4s, kUnroll independent multimem loads in flight per thread
+template <bool P2P>
 __global__ void __launch_bounds__(kThreadsNvls)
 nvls_reduce_adam_broadcast_kernel(NvlsComm c, float4* __restrict__ m, float4* __restrict__ v, const float4* __restrict__ w_local,
                                   size_t shard_off4, size_t n4, const long long* __restrict__ iterations, AdamHyper h,
@@ -83,7 +87,19 @@ nvls_reduce_adam_broadcast_kernel(NvlsComm c, float4* __restrict__ m, float4* __
 #pragma unroll
     for (int k = 0; k < kUnroll; ++k) {
       const size_t i = i0 + size_t(k) * stride;
-      if (i < n4) { G[k] = multimem_ld_reduce_add(reinterpret_cast<const float*>(g_mc + i)); W[k] = w_local[shard_off4 + i]; M[k] = m[shard_off4 + i]; V[k] = v[shard_off4 + i]; }
+      if (i < n4) {
+        if (P2P) {   // the replicas' gradients one by one, always in rank order (a shard is summed by exactly one rank)
+          float4 acc = __ldcg(reinterpret_cast<const float4*>(c.grads_peer[0]) + shard_off4 + i);
+          for (int r = 1; r < c.world; ++r) {
+            const float4 t4 = __ldcg(reinterpret_cast<const float4*>(c.grads_peer[r]) + shard_off4 + i);
+            acc.x += t4.x; acc.y += t4.y; acc.z += t4.z; acc.w += t4.w;
+          }
+          G[k] = acc;
+        } else {
+          G[k] = multimem_ld_reduce_add(reinterpret_cast<const float*>(g_mc + i));
+        }
+        W[k] = w_local[shard_off4 + i]; M[k] = m[shard_off4 + i]; V[k] = v[shard_off4 + i];
+      }
     }
 #pragma unroll
     for (int k = 0; k < kUnroll; ++k) {
@@ -97,7 +113,11 @@ nvls_reduce_adam_broadcast_kernel(NvlsComm c, float4* __restrict__ m, float4* __
       ADAM1(x) ADAM1(y) ADAM1(z) ADAM1(w)
 #undef ADAM1
       m[shard_off4 + i] = M[k]; v[shard_off4 + i] = V[k];
-      multimem_st(reinterpret_cast<float*>(w_mc + i), W[k]);   // every replica's copy of the weights, this one's included
+      if (P2P) {
+        for (int r = 0; r < c.world; ++r) __stcg(reinterpret_cast<float4*>(c.params_peer[r]) + shard_off4 + i, W[k]);
+      } else {
+        multimem_st(reinterpret_cast<float*>(w_mc + i), W[k]);   // every replica's copy of the weights, this one's included
+      }
     }
   }
   // ---- "done": once every CTA's stores are out, tell every replica
@@ -133,9 +153,14 @@ int nvls_reduce_adam_broadcast(const NvlsComm& c, float* w_local, float* m, floa
   const size_t n4 = n / 4;
   int grid = int(std::min<size_t>((n4 + size_t(kThreadsNvls) * kUnroll - 1) / (size_t(kThreadsNvls) * kUnroll), size_t(max_ctas > 0 ? max_ctas : 64)));
   if (grid < 1) grid = 1;
-  nvls_reduce_adam_broadcast_kernel<<<grid, kThreadsNvls, 0, stream>>>(c, reinterpret_cast<float4*>(m), reinterpret_cast<float4*>(v),
-                                                              reinterpret_cast<const float4*>(w_local), shard_off / 4, n4, iterations_dev, h,
-                                                              epoch_dev, cta_counter);
+  if (c.p2p)
+    nvls_reduce_adam_broadcast_kernel<true><<<grid, kThreadsNvls, 0, stream>>>(c, reinterpret_cast<float4*>(m), reinterpret_cast<float4*>(v),
+                                                                      reinterpret_cast<const float4*>(w_local), shard_off / 4, n4, iterations_dev, h,
+                                                                      epoch_dev, cta_counter);
+  else
+    nvls_reduce_adam_broadcast_kernel<false><<<grid, kThreadsNvls, 0, stream>>>(c, reinterpret_cast<float4*>(m), reinterpret_cast<float4*>(v),
+                                                                       reinterpret_cast<const float4*>(w_local), shard_off / 4, n4, iterations_dev, h,
+                                                                       epoch_dev, cta_counter);
   B200XF_CUDA(cudaGetLastError());
   nvls_wait_done_kernel<<<1, 32, 0, stream>>>(c, epoch_dev);
   B200XF_CUDA(cudaGetLastError());

@@ -115,16 +115,19 @@ class B200Strategy:
                 uid[0] = bytes(buf.raw)
             dist.broadcast_object_list(uid, src=0)
             model.comm_init(uid[0], self.rank, self.world_size)
-            # The fused NVLS update moves ~(1 + 1/W) bucket sizes per link direction where reduce-scatter + all-gather over
-            # point-to-point links move 2 (W-1)/W, and it needs fewer SMs the smaller the shard: measured faster on 8 replicas
-            # (4.55 -> 4.19 ms/step) and on 4 (4.48 -> 4.33), slower on 2 (profiles/r02_nvls_update.md).  B200XF_NVLS=1 / 0 forces it on / off.
+            # One fused kernel per bucket (reduce the rank's gradient shard over all replicas + Adam + write the new weights to every
+            # replica) over symmetric memory.  Through the NVSwitch (multimem) it moves ~(1 + 1/W) bucket sizes per link direction,
+            # point to point (W-1)/W (profiles/r02_nvls_update.md).
+            # B200XF_NVLS = auto | 1 (multimem) | p2p (point to point) | 0 (NCCL reduce-scatter / all-gather).
             mode = os.environ.get("B200XF_NVLS", "auto")
-            if mode == "1" or (mode not in ("0", "1") and self.world_size >= 4):
-                self._attach_nvls(model)
+            if mode == "auto":
+                mode = "1" if self.world_size >= 4 else "0"
+            if mode in ("1", "p2p"):
+                self._attach_nvls(model, point_to_point=(mode == "p2p"))
         self._models.append(model)
         return model
 
-    def _attach_nvls(self, model):
+    def _attach_nvls(self, model, point_to_point=False):
         """Move the model's flat weights and gradients into symmetric memory with a multicast (NVLS) mapping and switch the
         gradient exchange to the fused multimem kernel (reduce-scatter + Adam + all-gather in one launch).  Falls back to the
         NCCL path when the box offers no multicast mapping (B200XF_NVLS=0 forces that)."""
@@ -141,7 +144,7 @@ class B200Strategy:
             bufs = [symm_mem.empty(total, dtype=torch.float32, device=dev) for _ in range(2)]
             pad = symm_mem.empty(256, dtype=torch.int32, device=dev)
             handles = [symm_mem.rendezvous(t, group) for t in bufs + [pad]]
-            ok = all(int(h.multicast_ptr) != 0 for h in handles[:2])
+            ok = point_to_point or all(int(h.multicast_ptr) != 0 for h in handles[:2])
         except Exception as e:  # no symmetric memory on this build / box
             ok = False; why = repr(e)
         flag = torch.tensor([1 if ok else 0], device=model.device)
@@ -157,9 +160,9 @@ class B200Strategy:
         model._bind(model._ctx)                                  # the variable views now wrap the symmetric buffers
         torch.cuda.synchronize(model.device)
         dist.barrier()                                           # every replica's buffers and flag pad are initialised
-        pads = (C.c_void_p * self.world_size)(*[int(p) for p in handles[2].buffer_ptrs])
-        check(lib.b200xf_nvls_attach(model._ctx, C.c_void_p(int(handles[1].multicast_ptr)), C.c_void_p(int(handles[0].multicast_ptr)),
-                                     pads, self.rank, self.world_size))
+        arr = lambda h: (C.c_void_p * self.world_size)(*[int(p) for p in h.buffer_ptrs])
+        check(lib.b200xf_nvls_attach(model._ctx, C.c_void_p(int(handles[1].multicast_ptr) or None), C.c_void_p(int(handles[0].multicast_ptr) or None),
+                                     arr(handles[2]), arr(handles[1]), arr(handles[0]), int(point_to_point), self.rank, self.world_size))
         model._symmetric = (bufs, pad, handles)                  # keep the allocations alive as long as the model
         return True
 

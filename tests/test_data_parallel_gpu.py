@@ -119,7 +119,7 @@ def _oracle_run(world):
     return w0, oracle, grads, per_step
 
 
-MODES = [pytest.param({"B200XF_NVLS": "1"}, id="nvls-fused-update"),
+MODES = [pytest.param({"B200XF_NVLS": "1"}, id="nvls-fused-update"), pytest.param({"B200XF_NVLS": "p2p"}, id="p2p-fused-update"),
          pytest.param({"B200XF_NVLS": "0"}, id="nccl-sharded-pipelined-trailing"), pytest.param({"B200XF_NVLS": "0", "B200XF_PIPELINED_UPDATE": "1"}, id="nccl-pipelined-all"),
          pytest.param({"B200XF_NVLS": "0", "B200XF_PIPELINED_UPDATE": "0"}, id="nccl-sharded-chained"), pytest.param({"B200XF_SHARDED_UPDATE": "0"}, id="nccl-replicated-allreduce")]
 
@@ -132,7 +132,7 @@ def test_two_ranks_match_oracle_and_each_other(tmp_path, env):
     env = dict(env, B200XF_BUCKET_MB="1")
     mp.spawn(_rank_main, args=(world, _free_port(), str(tmp_path), env), nprocs=world, join=True)
     z = [np.load(tmp_path / f"rank{r}.npz") for r in range(world)]
-    if env.get("B200XF_NVLS") == "1":
+    if env.get("B200XF_NVLS") in ("1", "p2p"):
         assert int(z[0]["nvls"][0]) == 1, "the fused NVLS update was expected to be active on this box"
     names = [k for k in z[0].files if k[:2] in ("w|", "m|", "v|")]
     for k in names:  # mirrored variables and (after the gather) optimizer slots: identical on every replica
@@ -153,3 +153,32 @@ def test_two_ranks_match_oracle_and_each_other(tmp_path, env):
     mn = np.sqrt(sum(float(np.sum((z[0]["m|" + k.replace("/", "|")] - oracle.m[k]) ** 2)) for k in oracle.m))
     md = np.sqrt(sum(float(np.sum(oracle.m[k] ** 2)) for k in oracle.m))
     assert mn / md < 6e-2, mn / md
+
+
+def _two_contexts_main(out):
+    """One process, two GPUs, one context each (include/b200xf.h: "distinct contexts are independent"): every kernel that raises its
+    dynamic shared memory limit must do so on BOTH devices (cudaFuncSetAttribute is per device)."""
+    hp = dict(layers_count=1, embedding_size=512, heads_count=8, feed_forward_hidden_size=1024, input_vocabulary_size=3000,
+              target_vocabulary_size=3000, maximum_input_length=300, maximum_target_length=300, droput_rate=0.0)
+    res = []
+    for dev in ("cuda:0", "cuda:1"):
+        with torch.cuda.device(dev):
+            m = b200xf.Transformer(**hp, seed=3, device=dev)
+            m.iterations = 100
+            for S in (128, 260):   # single-tile and multi-tile attention kernels, d = 512 LayerNorm, >48 KB GEMM configurations
+                inp, tgt = b200xf.synthetic_batch(2, S, S + 1, 3000, 3000, seed=S, ragged=True)
+                res.append(m.train_step_device(inp, tgt, 1).cpu().numpy())
+            m.close()
+    np.save(out, np.stack(res))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_contexts_on_two_gpus_in_one_process(tmp_path):
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "two_ctx.npy")
+    p = mp.get_context("spawn").Process(target=_two_contexts_main, args=(out,))
+    p.start(); p.join(300)
+    assert p.exitcode == 0
+    r = np.load(out)
+    assert np.isfinite(r).all()
+    np.testing.assert_allclose(r[:2], r[2:], rtol=1e-5)   # the same model and batches give the same losses on either device
