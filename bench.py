@@ -409,6 +409,10 @@ def parity_block(model, name, cfg, hp, host_batch, world, rank, dist):
         flag = torch.tensor([1.0 if ok else 0.0], device="cuda")
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         ok = bool(flag.item() > 0.5)
+    if getattr(model, "_symmetric", None) is not None:   # fused NVLS update: no replica ever timed out at a cross-replica flag
+        from b200xf import _lib
+        out["nvls_error"] = int(_lib.load().b200xf_nvls_error(model._ctx))
+        ok = ok and out["nvls_error"] == 0
     out["ok"] = bool(ok)
     return out
 

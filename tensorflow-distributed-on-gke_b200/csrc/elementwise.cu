@@ -488,14 +488,16 @@ int embed_pe_fwd(const long long* tokens, const float* table, int vocab, const f
   return 0;
 }
 
+bool embed_sort_is_single_cta(int n, int vocab);
+
 size_t embed_bwd_scratch_bytes(int n) {
   size_t temp = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, temp, (const int*)nullptr, (int*)nullptr, (const int*)nullptr, (int*)nullptr, n);
   return align_up(temp, 256) + 4 * align_up(size_t(n) * sizeof(int), 256);
 }
 
-int embed_bwd(const long long* tokens, const bf16* dx, float* dtable, int vocab, int n, int d, void* scratch, size_t scratch_bytes,
-              cudaStream_t stream, DropArgs drop) {
+// phase 1: (token, position) pairs of the batch side sorted by token (positions ascending within a token) into the scratch
+int embed_bwd_sort(const long long* tokens, int vocab, int n, void* scratch, size_t scratch_bytes, cudaStream_t stream) {
   if (n <= 0) return 0;
   if (scratch_bytes < embed_bwd_scratch_bytes(n)) return set_error("embed_bwd: scratch too small");
   const size_t seg = align_up(size_t(n) * sizeof(int), 256);
@@ -506,22 +508,42 @@ int embed_bwd(const long long* tokens, const bf16* dx, float* dtable, int vocab,
   int* vals_out = reinterpret_cast<int*>(base + 3 * seg);
   void* temp = base + 4 * seg;
   size_t temp_bytes = scratch_bytes - 4 * seg;
-  if (n <= kSortMax && vocab < (1 << 19)) {
+  if (embed_sort_is_single_cta(n, vocab)) {
     if (n <= 1024) B200XF_CUDA(launch_k(embed_sort_kernel<1>, 1, kSortThreads, 0, stream, tokens, keys_out, vals_out, n, vocab));
     else if (n <= 2048) B200XF_CUDA(launch_k(embed_sort_kernel<2>, 1, kSortThreads, 0, stream, tokens, keys_out, vals_out, n, vocab));
     else B200XF_CUDA(launch_k(embed_sort_kernel<4>, 1, kSortThreads, 0, stream, tokens, keys_out, vals_out, n, vocab));
-    count_launch(-1);  // one launch instead of two
+    count_launch(1);
   } else {  // long-sequence batches: key extraction + device-wide radix sort
     B200XF_CUDA(launch_k(embed_keys_kernel, (n + 255) / 256, 256, 0, stream, tokens, keys_in, vals_in, n, vocab));
     int bits = 1;
     while ((1ll << bits) <= vocab) ++bits;
     B200XF_CUDA(cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, n, 0, bits, stream));
+    count_launch(2);
   }
+  B200XF_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// phase 2: the head of every run of equal tokens sums the run's gradient rows in order into the table's gradient
+int embed_bwd_sorted(const bf16* dx, float* dtable, int vocab, int n, int d, const void* scratch, cudaStream_t stream, DropArgs drop) {
+  if (n <= 0) return 0;
+  const size_t seg = align_up(size_t(n) * sizeof(int), 256);
+  const char* base = static_cast<const char*>(scratch);
+  const int* keys_out = reinterpret_cast<const int*>(base + seg);
+  const int* vals_out = reinterpret_cast<const int*>(base + 3 * seg);
   const int threads = min(256, max(32, (d / 4 + 31) / 32 * 32));
   B200XF_CUDA(launch_k(embed_bwd_kernel, n, threads, 0, stream, keys_out, vals_out, dx, dtable, n, d, vocab, sqrtf(float(d)), drop));
   B200XF_CUDA(cudaGetLastError());
-  count_launch(3);
+  count_launch(1);
   return 0;
+}
+
+bool embed_sort_is_single_cta(int n, int vocab) { return n <= kSortMax && vocab < (1 << 19); }
+
+int embed_bwd(const long long* tokens, const bf16* dx, float* dtable, int vocab, int n, int d, void* scratch, size_t scratch_bytes,
+              cudaStream_t stream, DropArgs drop) {
+  B200XF_TRY(embed_bwd_sort(tokens, vocab, n, scratch, scratch_bytes, stream));
+  return embed_bwd_sorted(dx, dtable, vocab, n, d, scratch, stream, drop);
 }
 
 namespace {
