@@ -807,12 +807,14 @@ attn_bwd_tc_multi_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
   if (warp == 1) { ptx::tmem_alloc(tmem_slot, 512); ptx::tmem_relinquish(); }
   pdl_wait();
   pdl_trigger();
+  int my_mask = 0;
   if (warp >= 2 && warp < 6) {
     const int j = threadIdx.x - 64;
-    s_mask[j] = (k0 + j >= p.Sk) ? 2 : (toks[k0 + j] == 0 ? 1 : 0);
+    my_mask = (k0 + j >= p.Sk) ? 2 : (toks[k0 + j] == 0 ? 1 : 0);
+    s_mask[j] = my_mask;
   }
   ptx::tc_fence_before();
-  __syncthreads();
+  const bool tile_masked = __syncthreads_or(my_mask != 0) != 0;   // this CTA's key tile holds a PAD key or runs past Sk
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tS = tmem, tdP = tmem + 128, tdQ = tmem + 256, tdK = tmem + 320, tdV = tmem + 384;
@@ -891,20 +893,32 @@ attn_bwd_tc_multi_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_
       load_stats(it + 1, m_nxt, l_nxt, d_nxt);   // in flight during this pair
       ptx::mbar_wait(s_ready, it & 1);
       ptx::tc_fence_after();
+      // a (query tile, key tile) pair with no PAD key and wholly below the causal diagonal needs no per-key test
+      const bool plain = !tile_masked && !(p.causal && k0 + kT - 1 > q0);
 #pragma unroll
       for (int c = half * 2; c < half * 2 + 2; ++c) {
         float sv[32], dp[32];
         tmem_ld32(tS + lane_base + c * 32, sv);
         tmem_ld32(tdP + lane_base + c * 32, dp);
+        if (plain) {
+          const float ml = -m_cur - l_cur;   // (finite here: a row that sees an unmasked key has a real maximum; rows past Sq carry m = +inf -> P = 0)
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int key = c * 32 + j;
-          const int mk = s_mask[key];
-          float v = sv[j] * p.scale_log2;
-          if (mk == 1 || (p.causal && k0 + key > q0 + i)) v = kMasked;
-          const float pr = (mk == 2) ? 0.f : ptx::fast_exp2((v - m_cur) - l_cur);
-          sv[j] = pr;
-          dp[j] = pr * (dp[j] - d_cur);
+          for (int j = 0; j < 32; ++j) {
+            const float pr = ptx::fast_exp2(fmaf(sv[j], p.scale_log2, ml));
+            sv[j] = pr;
+            dp[j] = pr * (dp[j] - d_cur);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int key = c * 32 + j;
+            const int mk = s_mask[key];
+            float v = sv[j] * p.scale_log2;
+            if (mk == 1 || (p.causal && k0 + key > q0 + i)) v = kMasked;
+            const float pr = (mk == 2) ? 0.f : ptx::fast_exp2((v - m_cur) - l_cur);
+            sv[j] = pr;
+            dp[j] = pr * (dp[j] - d_cur);
+          }
         }
         store_row32(sP, i, c * 32, sv);
         store_row32(sdS, i, c * 32, dp);
