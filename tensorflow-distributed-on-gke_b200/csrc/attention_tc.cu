@@ -102,12 +102,14 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
       ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
     }
   }
+  int my_mask = 0;
   if (warp >= 2 && warp < 6) {
     const int j = threadIdx.x - 64;
-    s_mask[j] = (j >= p.Sk) ? 2 : (p.key_tokens[size_t(b) * p.Sk + j] == 0 ? 1 : 0);
+    my_mask = (j >= p.Sk) ? 2 : (p.key_tokens[size_t(b) * p.Sk + j] == 0 ? 1 : 0);
+    s_mask[j] = my_mask;
   }
   ptx::tc_fence_before();
-  __syncthreads();
+  const bool plain = (__syncthreads_or(my_mask != 0) == 0) && !p.causal;   // no PAD key, Sk = 128, no look-ahead mask: no per-key test needed
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tS = tmem, tdP = tmem + 128, tdQ = tmem + 256, tdK = tmem + 320, tdV = tmem + 384;
@@ -156,19 +158,32 @@ attn_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     const bool row_ok = i < p.Sq;
     float s[64], dp[64];
     float mx = -INFINITY;
+    {   // this thread's 64 score and 64 dP columns: four TMEM loads behind ONE wait (a load round trip costs ~0.5 us)
+      uint32_t rs[64], rp[64];
 #pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      tmem_ld32(tS + lane_base + (half * 2 + c) * 32, s + c * 32);
-      tmem_ld32(tdP + lane_base + (half * 2 + c) * 32, dp + c * 32);
+      for (int c = 0; c < 2; ++c) {
+        ptx::tmem_ld_32x32(tS + lane_base + (half * 2 + c) * 32, rs + c * 32);
+        ptx::tmem_ld_32x32(tdP + lane_base + (half * 2 + c) * 32, rp + c * 32);
+      }
+      ptx::tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int key = (half * 2 + c) * 32 + j;
-        const int mk = s_mask[key];
-        float v = s[c * 32 + j] * p.scale_log2;
-        if (mk == 1 || (p.causal && key > i)) v = kMasked;
-        if (mk == 2) v = -INFINITY;
-        s[c * 32 + j] = v;
-        mx = fmaxf(mx, v);
+      for (int j = 0; j < 64; ++j) dp[j] = __uint_as_float(rp[j]);
+      if (plain) {
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+        for (int j = 0; j < 64; ++j) { s[j] = __uint_as_float(rs[j]) * p.scale_log2; m4[j & 3] = fmaxf(m4[j & 3], s[j]); }
+        mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+      } else {
+#pragma unroll
+        for (int j = 0; j < 64; ++j) {
+          const int key = half * 64 + j;
+          const int mk = s_mask[key];
+          float v = __uint_as_float(rs[j]) * p.scale_log2;
+          if (mk == 1 || (p.causal && key > i)) v = kMasked;
+          if (mk == 2) v = -INFINITY;
+          s[j] = v;
+          mx = fmaxf(mx, v);
+        }
       }
     }
     xch[half * kT + i] = mx;
@@ -266,12 +281,14 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
       ptx::tma_load_2d(sV, &tm_v, &bars[0], h * kD, b * p.Sk);
     }
   }
+  int my_mask = 0;
   if (warp >= 2) {
     const int j = threadIdx.x - 64;
-    s_mask[j] = (j >= p.Sk) ? 2 : (p.key_tokens[size_t(b) * p.Sk + j] == 0 ? 1 : 0);
+    my_mask = (j >= p.Sk) ? 2 : (p.key_tokens[size_t(b) * p.Sk + j] == 0 ? 1 : 0);
+    s_mask[j] = my_mask;
   }
   ptx::tc_fence_before();
-  __syncthreads();
+  const bool plain = (__syncthreads_or(my_mask != 0) == 0) && !p.causal;   // no PAD key, Sk = 128, no look-ahead mask: no per-key test needed
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tS = tmem, tO = tmem + 128;
@@ -304,23 +321,32 @@ attn_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_consta
     const bool row_ok = i < p.Sq;
     float s[kT];
     float mx = -INFINITY;
+    {   // the whole 128-column score row: four TMEM loads behind ONE wait
+      uint32_t rs[kT];
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      tmem_ld32(tS + lane_base + c * 32, s + c * 32);
+      for (int c = 0; c < 4; ++c) ptx::tmem_ld_32x32(tS + lane_base + c * 32, rs + c * 32);
+      ptx::tmem_ld_wait();
+      if (plain) {
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int key = c * 32 + j;
-        const int mk = s_mask[key];
-        float v = s[key] * p.scale_log2;
-        if (mk == 1 || (p.causal && key > i)) v = kMasked;
-        if (mk == 2) v = -INFINITY;
-        s[key] = v;
-        mx = fmaxf(mx, v);
+        for (int j = 0; j < kT; ++j) { s[j] = __uint_as_float(rs[j]) * p.scale_log2; m4[j & 3] = fmaxf(m4[j & 3], s[j]); }
+        mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+      } else {
+#pragma unroll
+        for (int key = 0; key < kT; ++key) {
+          const int mk = s_mask[key];
+          float v = __uint_as_float(rs[key]) * p.scale_log2;
+          if (mk == 1 || (p.causal && key > i)) v = kMasked;
+          if (mk == 2) v = -INFINITY;
+          s[key] = v;
+          mx = fmaxf(mx, v);
+        }
       }
     }
-    float sum = 0.f;
+    float s4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int j = 0; j < kT; ++j) { s[j] = ptx::fast_exp2(s[j] - mx); sum += s[j]; }
+    for (int j = 0; j < kT; ++j) { s[j] = ptx::fast_exp2(s[j] - mx); s4[j & 3] += s[j]; }
+    const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
 #pragma unroll
     for (int c = 0; c < 4; ++c) store_row32(sP, i, c * 32, s + c * 32);
     ptx::tc_fence_before();
