@@ -121,3 +121,78 @@ def test_argmax_first_max_wins():
     assert (num, den) == (1, 1)
     num, den = O.accuracy_counts(torch.tensor([[2]]), x)
     assert (num, den) == (0, 1)
+
+
+def test_sdpa_closed_form_kat():  # transformer_model.py:73-109 on operands whose softmax is (numerically) one-hot or an exact tie
+    k = torch.tensor([[10., 0, 0], [0, 10, 0], [0, 0, 10], [0, 0, 10]])
+    v = torch.tensor([[1., 0], [10, 0], [100, 5], [1000, 6]])
+    m = O.OracleTransformer(1, 4, 1, 4, 8, 8, 8, 8)
+    for q, w_want, o_want in (([[0., 10, 0]], [[0, 1, 0, 0]], [[10, 0]]),
+                              ([[0., 0, 10]], [[0, 0, .5, .5]], [[550, 5.5]]),
+                              ([[10., 10, 0]], [[.5, .5, 0, 0]], [[5.5, 0]])):
+        o, w = m._sdpa(torch.tensor(q), k, v, None)
+        np.testing.assert_allclose(w.numpy(), w_want, atol=1e-6)     # e^(-100/sqrt(3)) ~ 1e-25 off a one-hot
+        np.testing.assert_allclose(o.numpy(), o_want, rtol=1e-6, atol=1e-20)
+    # a masked key gets exactly zero weight in fp32 (additive -1e9, :101-102), whatever its score
+    o, w = m._sdpa(torch.tensor([[0., 0, 10]]), k, v, torch.tensor([[0., 0, 0, 1]]))
+    assert w[0, 3].item() == 0.0 and w[0, 2].item() == 1.0
+    np.testing.assert_allclose(o.numpy(), [[100, 5]], rtol=1e-6)
+
+
+def test_forward_matches_an_independent_implementation_of_the_architecture():
+    """Not a pin to the reference (TensorFlow cannot run here): a cross-check of the restatement against torch.nn's own,
+    independently written post-LayerNorm encoder / decoder stacks with the SAME weights -- head split and merge order, the
+    1/sqrt(dk) scaling, where the residuals and LayerNorms sit, epsilon, biased variance, ReLU feed-forward, key-padding and
+    look-ahead masking (transformer_model.py:112-166,178-248).  Embedding, sqrt(d) scaling and positional encoding are the
+    oracle's own on both sides (torch.nn has none)."""
+    import torch.nn as nn
+    L, d, H, dff, V = 2, 32, 4, 64, 50
+    model = O.OracleTransformer(L, d, H, dff, V, V, 64, 64).load(
+        {n: a + (0.1 * np.random.default_rng(5).standard_normal(a.shape).astype(np.float32) if a.ndim == 1 else 0)
+         for n, a in O.init_parameters(L, d, dff, V, V, seed=3).items()})   # non-trivial biases, gammas, betas
+    P = {n: t.detach() for n, t in model.params.items()}
+    enc = nn.TransformerEncoder(nn.TransformerEncoderLayer(d, H, dff, dropout=0.0, activation="relu", layer_norm_eps=1e-6,
+                                                           batch_first=True, norm_first=False), L, enable_nested_tensor=False)
+    dec = nn.TransformerDecoder(nn.TransformerDecoderLayer(d, H, dff, dropout=0.0, activation="relu", layer_norm_eps=1e-6,
+                                                           batch_first=True, norm_first=False), L)
+
+    def put_mha(mod, prefix):   # nn.MultiheadAttention packs q | k | v as rows of in_proj_weight [3d, d] (y = x W^T + b)
+        g = lambda n: P[f"{prefix}/{n}"]
+        mod.in_proj_weight.data = torch.cat([g("query_generator_weights/kernel").T, g("key_generator_weights/kernel").T,
+                                             g("value_generator_weights/kernel").T])
+        mod.in_proj_bias.data = torch.cat([g("query_generator_weights/bias"), g("key_generator_weights/bias"), g("value_generator_weights/bias")])
+        mod.out_proj.weight.data = g("dense/kernel").T.contiguous(); mod.out_proj.bias.data = g("dense/bias").clone()
+
+    def put(lin_or_ln, prefix, dense=True):
+        if dense:
+            lin_or_ln.weight.data = P[prefix + "/kernel"].T.contiguous(); lin_or_ln.bias.data = P[prefix + "/bias"].clone()
+        else:
+            lin_or_ln.weight.data = P[prefix + "/gamma"].clone(); lin_or_ln.bias.data = P[prefix + "/beta"].clone()
+
+    for i, lyr in enumerate(enc.layers):
+        p = f"encoder/encoder_layers/{i}"
+        put_mha(lyr.self_attn, p + "/mha")
+        put(lyr.linear1, p + "/ffn/layer_with_weights-0"); put(lyr.linear2, p + "/ffn/layer_with_weights-1")
+        put(lyr.norm1, p + "/layernorm1", False); put(lyr.norm2, p + "/layernorm2", False)
+    for i, lyr in enumerate(dec.layers):
+        p = f"decoder/decoder_layers/{i}"
+        put_mha(lyr.self_attn, p + "/mha1"); put_mha(lyr.multihead_attn, p + "/mha2")
+        put(lyr.linear1, p + "/ffn/layer_with_weights-0"); put(lyr.linear2, p + "/ffn/layer_with_weights-1")
+        for k in (1, 2, 3):
+            put(getattr(lyr, f"norm{k}"), p + f"/layernorm{k}", False)
+    enc.train(); dec.train()    # dropout is 0; training mode keeps torch on its plain (non-fused) code path
+
+    inp, tgt = (torch.as_tensor(a) for a in O.synthetic_batch(3, 11, 10, V, V, seed=2, ragged=True))
+    tgt = tgt[:, :-1]
+    with torch.no_grad():
+        want, _ = model([inp, tgt])
+        emb = lambda name, tok, pe: P[name][tok] * np.sqrt(np.float32(d)) + pe[:, :tok.shape[1], :]
+        src_pad, tgt_pad = inp == 0, tgt == 0
+        memory = enc(emb("encoder/embedding/embeddings", inp, model.pe_in), src_key_padding_mask=src_pad)
+        causal = torch.triu(torch.ones(tgt.shape[1], tgt.shape[1], dtype=torch.bool), 1)
+        out = dec(emb("decoder/embedding/embeddings", tgt, model.pe_tgt), memory, tgt_mask=causal, tgt_key_padding_mask=tgt_pad,
+                  memory_key_padding_mask=src_pad)
+        got = out @ P["final_layer/kernel"] + P["final_layer/bias"]
+    valid = ~tgt_pad                                   # rows whose query is PAD are never used by the loss (transformer_model.py:11-17)
+    assert valid.sum() > 10 and src_pad.any() and tgt_pad.any()
+    np.testing.assert_allclose(got[valid].numpy(), want[valid].numpy(), rtol=2e-4, atol=2e-5)
