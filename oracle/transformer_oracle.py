@@ -10,7 +10,8 @@ network); the reference ships no tests, golden vectors or fixtures for this path
 checkpoint data shards are missing (.MISSING_LARGE_BLOBS).  What *is* pinned: the closed-form
 known answers derivable from the reference source (tests/test_oracle_kat.py) and the
 parameter names/shapes/offsets decoded from saved_weights/2/model_weights.index
-(tests/golden/param_table.json).
+(tests/golden/param_table.json).  The forward pass is also cross-checked against torch.nn's own encoder /
+decoder stacks with the same weights (same test file): a guard against slips in the restatement, not a pin.
 
 Every function cites the reference file:line it restates (paths are relative to
 /root/reference/distributed_training_transformer/).  torch is used as a CPU fp32 array
