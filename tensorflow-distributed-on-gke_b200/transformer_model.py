@@ -360,6 +360,7 @@ class Transformer:
         T1 = target.shape[1]
         self._ensure_built(max(B * S, B * T1))
         self._sync_weights()
+        self._forward_serial += 1
         out = (C.c_float * 6)()
         check(_lib.load().b200xf_train_step_host(self._ctx, C.c_void_p(inp.data_ptr()), C.c_void_p(target.data_ptr()), B, S, T1,
                                                  int(workers_count), out))
