@@ -182,3 +182,32 @@ def test_two_contexts_on_two_gpus_in_one_process(tmp_path):
     r = np.load(out)
     assert np.isfinite(r).all()
     np.testing.assert_allclose(r[:2], r[2:], rtol=1e-5)   # the same model and batches give the same losses on either device
+
+
+def _launched_worker(out_dir):
+    """What a worker of the reference's __main__.py does, started by b200xf.launch instead of Kubernetes (cluster/cluster.py:12-79)."""
+    cluster = b200xf.B200Cluster(2)
+    strategy = cluster.execution_strategy()
+    rank = cluster.worker_index
+    with strategy.scope():
+        model = b200xf.Transformer(**HP, seed=4, device=f"cuda:{rank}")
+        optimizer = b200xf.Adam(b200xf.TransformerLearningRateSchedule(HP["embedding_size"]), beta_1=0.9, beta_2=0.98, epsilon=1e-9)
+        b200xf.build_model(model)
+        strategy.attach(model)
+        step = b200xf.make_distributed_train_step(strategy, b200xf.make_train_step(model, optimizer, cluster.worker_count))
+    model.iterations = 200
+    batches = [b200xf.synthetic_batch(8, 20, 19, 203, 157, seed=90 + i, ragged=True) for i in range(3)]
+    losses = [float(step(inp, tgt)) for inp, tgt in strategy.experimental_distribute_dataset(batches)]
+    np.savez(os.path.join(out_dir, f"launched{rank}.npz"), losses=np.array(losses), chief=np.array([int(cluster.chief())]),
+             w=np.concatenate([a.ravel() for a in model.get_weights_dict().values()]))
+    model.close()
+    cluster.shutdown()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_launcher_and_cluster_drive_two_gpus(tmp_path):
+    b200xf.launch(2, _launched_worker, args=(str(tmp_path),))
+    z = [np.load(tmp_path / f"launched{r}.npz") for r in range(2)]
+    assert [int(f["chief"][0]) for f in z] == [1, 0]
+    np.testing.assert_allclose(z[0]["losses"], z[1]["losses"], rtol=1e-6)   # the SUM over replicas, the same on both
+    assert np.isfinite(z[0]["losses"]).all() and np.array_equal(z[0]["w"], z[1]["w"])
